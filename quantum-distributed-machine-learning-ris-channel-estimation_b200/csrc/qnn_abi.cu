@@ -1,0 +1,206 @@
+// C ABI of libqnn_b200.so (include/qnn_b200.h): circuit lowering and kernel dispatch.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "qnn_internal.h"
+
+static thread_local char g_err[512] = "";
+
+void qnn_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+extern "C" const char* qnn_last_error(void) { return g_err; }
+extern "C" int32_t qnn_abi_version(void) { return QNN_ABI_VERSION; }
+
+static int n_angles(int kind) {
+  switch (kind) {
+    case QNN_RX: case QNN_RY: case QNN_RZ: return 1;
+    case QNN_U3: case QNN_CU3: return 3;
+    case QNN_CNOT: case QNN_CZ: return 0;
+    default: return -1;
+  }
+}
+static bool two_qubit(int kind) { return kind == QNN_CNOT || kind == QNN_CZ || kind == QNN_CU3; }
+
+extern "C" int qnn_circuit_create(const qnn_op* ops, int32_t n_ops, int32_t n_qubits, int32_t n_inputs,
+                                  int32_t n_weights, int32_t encoder, qnn_circuit** out) {
+  if (!out) { qnn_set_error("qnn_circuit_create: out is NULL"); return QNN_ERR_INVALID; }
+  *out = nullptr;
+  if (n_qubits < 1 || n_qubits > QNN_MAX_QUBITS) {
+    qnn_set_error("n_qubits=%d outside [1, %d]", n_qubits, QNN_MAX_QUBITS);
+    return QNN_ERR_INVALID;
+  }
+  if (n_ops < 0 || (n_ops > 0 && !ops) || n_inputs < 0 || n_weights < 0) {
+    qnn_set_error("bad n_ops/n_inputs/n_weights (%d/%d/%d) or NULL ops", n_ops, n_inputs, n_weights);
+    return QNN_ERR_INVALID;
+  }
+  if (encoder != QNN_ENC_NONE && encoder != QNN_ENC_AMPLITUDE) {
+    qnn_set_error("unknown encoder %d", encoder);
+    return QNN_ERR_INVALID;
+  }
+  if (encoder == QNN_ENC_AMPLITUDE && n_inputs < 1) {
+    qnn_set_error("amplitude encoder needs n_inputs >= 1");
+    return QNN_ERR_INVALID;
+  }
+  if (encoder == QNN_ENC_NONE && n_inputs > 4096) {
+    qnn_set_error("n_inputs=%d > 4096 angle inputs", n_inputs);
+    return QNN_ERR_INVALID;
+  }
+  qnn_circuit* c = new (std::nothrow) qnn_circuit();
+  if (!c) { qnn_set_error("out of host memory"); return QNN_ERR_INVALID; }
+  c->n_qubits = n_qubits; c->n_inputs = n_inputs; c->n_weights = n_weights; c->encoder = encoder;
+  c->ops.assign(ops, ops + n_ops);
+  for (int i = 0; i < n_ops; ++i) {
+    const qnn_op& o = ops[i];
+    const int na = n_angles(o.kind);
+    if (na < 0) { qnn_set_error("op %d: unknown gate kind %d", i, o.kind); delete c; return QNN_ERR_INVALID; }
+    const bool two = two_qubit(o.kind);
+    if (o.wire0 < 0 || o.wire0 >= n_qubits || (two && (o.wire1 < 0 || o.wire1 >= n_qubits || o.wire1 == o.wire0))) {
+      qnn_set_error("op %d: wires (%d, %d) invalid for %d qubits", i, o.wire0, o.wire1, n_qubits);
+      delete c; return QNN_ERR_INVALID;
+    }
+    DevOp d{};
+    d.kind = o.kind;
+    const int target = two ? o.wire1 : o.wire0;
+    d.tpos = n_qubits - 1 - target;
+    d.cpos = two ? n_qubits - 1 - o.wire0 : -1;
+    d.nang = na;
+    d.coef = -1; d.slot = -1;
+    bool any_x = false, any_w = false;
+    for (int k = 0; k < 3; ++k) { d.src[k] = QNN_SRC_CONST; d.value[k] = 0.f; }
+    for (int k = 0; k < na; ++k) {
+      const int s = o.src[k];
+      d.src[k] = s; d.value[k] = o.value[k];
+      if (s == QNN_SRC_CONST) continue;
+      if (s >= 0) {
+        if (s >= n_weights) { qnn_set_error("op %d: weight index %d >= n_weights %d", i, s, n_weights); delete c; return QNN_ERR_INVALID; }
+        any_w = true;
+      } else {
+        const int j = -1 - s;
+        if (encoder == QNN_ENC_AMPLITUDE) { qnn_set_error("op %d: input-sourced angles cannot be combined with the amplitude encoder", i); delete c; return QNN_ERR_INVALID; }
+        if (j >= n_inputs) { qnn_set_error("op %d: input column %d >= n_inputs %d", i, j, n_inputs); delete c; return QNN_ERR_INVALID; }
+        any_x = true;
+      }
+    }
+    d.mode = (na == 0) ? 0 : (any_x ? 2 : 1);
+    if (d.mode == 1) d.coef = c->n_coef++;
+    if (any_w) {
+      d.slot = c->n_slots;
+      for (int k = 0; k < na; ++k) c->slot_w.push_back(d.src[k] >= 0 ? d.src[k] : -1);
+      c->n_slots += na;
+    }
+    c->dev_ops_h.push_back(d);
+  }
+  // CSR weight -> slots
+  std::vector<int32_t> ptr(n_weights + 1, 0), idx;
+  for (int s = 0; s < c->n_slots; ++s) if (c->slot_w[s] >= 0) ptr[c->slot_w[s] + 1]++;
+  for (int i = 0; i < n_weights; ++i) ptr[i + 1] += ptr[i];
+  idx.resize(ptr[n_weights]);
+  { std::vector<int32_t> fill(ptr.begin(), ptr.end() - 1);
+    for (int s = 0; s < c->n_slots; ++s) if (c->slot_w[s] >= 0) idx[fill[c->slot_w[s]]++] = s; }
+
+  cudaError_t e = cudaGetDevice(&c->device);
+  if (e != cudaSuccess) { qnn_set_error("cudaGetDevice failed: %s (is a CUDA device present?)", cudaGetErrorString(e)); delete c; return QNN_ERR_CUDA; }
+  auto upload = [&](void** dptr, const void* src, size_t bytes) -> cudaError_t {
+    cudaError_t err = cudaMalloc(dptr, bytes ? bytes : 16);
+    if (err != cudaSuccess) return err;
+    return bytes ? cudaMemcpy(*dptr, src, bytes, cudaMemcpyHostToDevice) : cudaSuccess;
+  };
+  if ((e = upload((void**)&c->d_ops, c->dev_ops_h.data(), c->dev_ops_h.size() * sizeof(DevOp))) != cudaSuccess ||
+      (e = upload((void**)&c->d_slot_ptr, ptr.data(), ptr.size() * sizeof(int32_t))) != cudaSuccess ||
+      (e = upload((void**)&c->d_slot_idx, idx.data(), idx.size() * sizeof(int32_t))) != cudaSuccess) {
+    qnn_set_error("uploading the lowered circuit failed: %s", cudaGetErrorString(e));
+    qnn_circuit_destroy(c);
+    return QNN_ERR_CUDA;
+  }
+  *out = c;
+  return QNN_OK;
+}
+
+extern "C" void qnn_circuit_destroy(qnn_circuit* c) {
+  if (!c) return;
+  if (c->d_ops) cudaFree(c->d_ops);
+  if (c->d_slot_ptr) cudaFree(c->d_slot_ptr);
+  if (c->d_slot_idx) cudaFree(c->d_slot_idx);
+  delete c;
+}
+
+extern "C" int32_t qnn_circuit_n_qubits(const qnn_circuit* c) { return c ? c->n_qubits : -1; }
+extern "C" int32_t qnn_circuit_n_inputs(const qnn_circuit* c) { return c ? c->n_inputs : -1; }
+extern "C" int32_t qnn_circuit_n_weights(const qnn_circuit* c) { return c ? c->n_weights : -1; }
+
+extern "C" const char* qnn_circuit_plan(const qnn_circuit* c, int64_t B) {
+  if (!c) return "";
+  GenericPlan p;
+  generic_plan(c, B, &p);
+  c->plan_name = p.name;
+  return c->plan_name.c_str();
+}
+
+extern "C" int32_t qnn_forward_launches(const qnn_circuit* c, int64_t) {
+  if (!c) return 0;
+  return 1 + (c->n_coef > 0 ? 1 : 0);
+}
+extern "C" int32_t qnn_backward_launches(const qnn_circuit* c, int64_t) {
+  if (!c) return 0;
+  return 1 + (c->n_coef > 0 ? 1 : 0) + (c->n_weights > 0 ? 1 : 0);
+}
+
+extern "C" size_t qnn_forward_workspace_bytes(const qnn_circuit* c, int64_t B) {
+  if (!c || B <= 0) return 0;
+  GenericPlan p;
+  generic_plan(c, B, &p);
+  return p.ws_coef + p.ws_state_fwd;
+}
+extern "C" size_t qnn_backward_workspace_bytes(const qnn_circuit* c, int64_t B) {
+  if (!c || B <= 0) return 0;
+  GenericPlan p;
+  generic_plan(c, B, &p);
+  return p.ws_coef + p.ws_state_bwd + p.ws_partial;
+}
+
+static int check_common(const char* fn, const qnn_circuit* c, const float* x, const float* w, int64_t B) {
+  if (!c) { qnn_set_error("%s: circuit is NULL", fn); return QNN_ERR_INVALID; }
+  if (B <= 0) { qnn_set_error("%s: B=%lld must be positive", fn, (long long)B); return QNN_ERR_INVALID; }
+  if (!x && c->n_inputs > 0) { qnn_set_error("%s: x is NULL", fn); return QNN_ERR_INVALID; }
+  if (!w && c->n_weights > 0) { qnn_set_error("%s: w is NULL", fn); return QNN_ERR_INVALID; }
+  return QNN_OK;
+}
+
+extern "C" int qnn_forward(const qnn_circuit* c, const float* x, const float* w, float* y, int64_t B,
+                           void* workspace, size_t workspace_bytes, void* cuda_stream) {
+  int rc = check_common("qnn_forward", c, x, w, B);
+  if (rc) return rc;
+  if (!y) { qnn_set_error("qnn_forward: y is NULL"); return QNN_ERR_INVALID; }
+  GenericPlan p;
+  generic_plan(c, B, &p);
+  const size_t need = p.ws_coef + p.ws_state_fwd;
+  if (need > 0 && (!workspace || workspace_bytes < need)) {
+    qnn_set_error("qnn_forward: workspace of %zu bytes needed, %zu given", need, workspace ? workspace_bytes : (size_t)0);
+    return QNN_ERR_WORKSPACE;
+  }
+  return generic_forward(c, p, x, w, y, B, workspace, static_cast<cudaStream_t>(cuda_stream));
+}
+
+extern "C" int qnn_backward(const qnn_circuit* c, const float* x, const float* w, const float* gy,
+                            float* gx, float* gw, int64_t B, void* workspace, size_t workspace_bytes,
+                            void* cuda_stream) {
+  int rc = check_common("qnn_backward", c, x, w, B);
+  if (rc) return rc;
+  if (!gy) { qnn_set_error("qnn_backward: gy is NULL"); return QNN_ERR_INVALID; }
+  if (!gw && c->n_weights > 0) { qnn_set_error("qnn_backward: gw is NULL"); return QNN_ERR_INVALID; }
+  GenericPlan p;
+  generic_plan(c, B, &p);
+  const size_t need = p.ws_coef + p.ws_state_bwd + p.ws_partial;
+  if (!workspace || workspace_bytes < need) {
+    qnn_set_error("qnn_backward: workspace of %zu bytes needed, %zu given", need, workspace ? workspace_bytes : (size_t)0);
+    return QNN_ERR_WORKSPACE;
+  }
+  return generic_backward(c, p, x, w, gy, gx, gw, B, workspace, static_cast<cudaStream_t>(cuda_stream));
+}

@@ -1,0 +1,153 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the CPU oracle on the same
+seeded inputs; the committed golden vectors; size-independent properties at BASELINE sizes."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import qris_b200
+from helpers import REL_TOL, assert_close, oracle_ops, seeded_inputs
+from oracle import qnn_oracle as O
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "qnn_golden.npz")
+
+
+def run_gpu(circ, x, w, gy):
+    dev = torch.device("cuda:0")
+    xd, wd, gd = x.to(dev), w.to(dev), gy.to(dev)
+    y = qris_b200.qnn_forward_raw(circ, xd, wd)
+    gx, gw = qris_b200.qnn_backward_raw(circ, xd, wd, gd)
+    torch.cuda.synchronize()
+    return y.cpu().numpy(), gx.cpu().numpy(), gw.cpu().numpy()
+
+
+def check_against_oracle(circ, B, seed=0):
+    x, w, gy = seeded_inputs(circ, B, seed)
+    y, gx, gw = run_gpu(circ, x, w, gy)
+    yo, gxo, gwo = O.forward_and_grads(oracle_ops(circ), circ.n_qubits, x, w, gy, encoder=circ.encoder)
+    assert_close(y, yo.numpy(), what="y")
+    assert_close(gx, gxo.numpy(), scale=float(np.abs(gxo.numpy()).max()), what="gx")
+    # gw sums B per-sample terms: fp32 error scales with the magnitude of what is summed
+    assert_close(gw, gwo.numpy(), scale=float(np.abs(gwo.numpy()).max()), what="gw")
+
+
+@pytest.mark.parametrize("n,L,B", [(1, 2, 5), (2, 1, 7), (3, 3, 33), (4, 3, 256), (6, 3, 256), (6, 3, 1),
+                                    (8, 3, 64), (10, 3, 40), (10, 1, 3)])
+def test_reference_circuit_parity(n, L, B):
+    check_against_oracle(qris_b200.reference_circuit(n, L), B, seed=n * 100 + L)
+
+
+@pytest.mark.parametrize("n,L,B", [(2, 2, 9), (5, 2, 64), (7, 1, 31), (10, 3, 24)])
+def test_u3cu3_circuit_parity(n, L, B):
+    check_against_oracle(qris_b200.u3cu3_circuit(n, L), B, seed=n * 100 + L)
+
+
+@pytest.mark.parametrize("n,L,B", [(3, 2, 17), (8, 1, 12), (10, 1, 5)])
+def test_amplitude_encoder_parity(n, L, B):
+    check_against_oracle(qris_b200.u3cu3_circuit(n, L, encoder="amplitude"), B, seed=n)
+
+
+@pytest.mark.parametrize("n,L,B", [(11, 2, 5), (12, 1, 3), (13, 1, 2)])
+def test_cta_per_sample_sizes(n, L, B):
+    check_against_oracle(qris_b200.u3cu3_circuit(n, L), B, seed=n)
+    check_against_oracle(qris_b200.reference_circuit(n, L), B, seed=n + 1)
+
+
+@pytest.mark.parametrize("n,B", [(14, 2), (16, 1)])
+def test_largest_sizes(n, B):
+    """n = 16 is QNN_MAX_QUBITS (BASELINE config 4's width): 512 KiB of state per sample."""
+    check_against_oracle(qris_b200.u3cu3_circuit(n, 1), B, seed=n)
+
+
+def test_mixed_sources_reupload_and_constants():
+    """Input columns used twice (data re-uploading), constants, shared weights, RX and CZ."""
+    Op = qris_b200.Op
+    ops = [Op("RX", (0,), (("x", 0),)), Op("RY", (1,), (("x", 1),)), Op("RZ", (2,), (("x", 0),)),
+           Op("U3", (2,), (("x", 2), ("w", 0), ("c", 0.3))), Op("CZ", (0, 2)), Op("CNOT", (2, 1)),
+           Op("RY", (0,), (("w", 1),)), Op("RY", (1,), (("w", 1),)), Op("CU3", (1, 0), (("w", 2), ("x", 1), ("w", 0))),
+           Op("RX", (2,), (("c", -1.1),)), Op("RZ", (1,), (("w", 3),)), Op("RX", (1,), (("w", 4),))]
+    circ = qris_b200.Circuit(3, ops, n_inputs=3, n_weights=5)
+    check_against_oracle(circ, 50, seed=9)
+
+
+def test_golden_vectors():
+    g = np.load(GOLDEN)
+    for name in sorted({k.split("/")[0] for k in g.files}):
+        n, L, B, enc = (int(v) for v in g[f"{name}/meta"])
+        circ = (qris_b200.reference_circuit(n, L) if name.startswith("ref")
+                else qris_b200.u3cu3_circuit(n, L, encoder="amplitude" if enc else "angle"))
+        y, gx, gw = run_gpu(circ, torch.tensor(g[f"{name}/x"]), torch.tensor(g[f"{name}/w"]), torch.tensor(g[f"{name}/gy"]))
+        assert_close(y, g[f"{name}/y"], what=f"{name} y")
+        assert_close(gx, g[f"{name}/gx"], scale=float(np.abs(g[f"{name}/gx"]).max()), what=f"{name} gx")
+        assert_close(gw, g[f"{name}/gw"], scale=float(np.abs(g[f"{name}/gw"]).max()), what=f"{name} gw")
+
+
+def test_survey_fixed_vector_and_closed_form():
+    x, W = O.survey_fixed_inputs()
+    fv = O.SURVEY_FIXED_VECTOR
+    circ = qris_b200.reference_circuit(6, 3)
+    y, gx, gw = run_gpu(circ, torch.tensor(x, dtype=torch.float32), torch.tensor(W.reshape(-1), dtype=torch.float32),
+                        torch.tensor([fv["g"]], dtype=torch.float32))
+    assert_close(y[0], np.array(fv["y"]), what="fixed y")
+    gW = gw.reshape(3, 6, 2)
+    assert abs(gx[0, 0] - fv["dx0"]) < 1e-5 and abs(gW[1, 2, 0] - fv["dW_1_2_0"]) < 2e-5
+    assert abs(gW[2, 3, 0] - fv["dW_2_3_0"]) < 1e-5 and abs(gW[2, 3, 1]) < 1e-6
+    # analytic L = 1 closed form, at a BASELINE-sized batch
+    rng = np.random.default_rng(0)
+    xx = rng.uniform(-1, 1, (4096, 6)).astype(np.float32); ww = rng.uniform(0, 2 * np.pi, (1, 6, 2)).astype(np.float32)
+    c1 = qris_b200.reference_circuit(6, 1)
+    y1 = qris_b200.qnn_forward_raw(c1, torch.tensor(xx).cuda(), torch.tensor(ww.reshape(-1)).cuda()).cpu().numpy()
+    assert_close(y1, O.ref_circuit_L1_closed_form(xx, ww), what="closed form")
+
+
+@pytest.mark.parametrize("kind,n,L,B", [("ref", 6, 3, 4096), ("u3", 10, 3, 65536)])
+def test_full_size_properties(kind, n, L, B):
+    """BASELINE configs 2 and 3 at full batch: properties that need no oracle run of that size."""
+    circ = qris_b200.reference_circuit(n, L) if kind == "ref" else qris_b200.u3cu3_circuit(n, L)
+    x, w, gy = seeded_inputs(circ, B, seed=42)
+    dev = torch.device("cuda:0")
+    xd, wd, gd = x.to(dev), w.to(dev), gy.to(dev)
+    y = qris_b200.qnn_forward_raw(circ, xd, wd)
+    assert torch.isfinite(y).all() and y.abs().max() <= 1 + 1e-5
+    gx, gw = qris_b200.qnn_backward_raw(circ, xd, wd, gd)
+    # (1) per-sample independence: any row subset reproduces the same rows
+    idx = torch.tensor([0, 1, B // 3, B // 2 + 1, B - 1], device=dev)
+    ys = qris_b200.qnn_forward_raw(circ, xd[idx].contiguous(), wd)
+    gxs, _ = qris_b200.qnn_backward_raw(circ, xd[idx].contiguous(), wd, gd[idx].contiguous())
+    assert torch.equal(ys, y[idx]) and torch.allclose(gxs, gx[idx], atol=1e-6)
+    # (2) those rows agree with the oracle
+    yo, gxo, _ = O.forward_and_grads(oracle_ops(circ), n, x[idx.cpu()], w, gy[idx.cpu()])
+    assert_close(ys.cpu().numpy(), yo.numpy(), what="rows y")
+    assert_close(gxs.cpu().numpy(), gxo.numpy(), scale=float(gxo.abs().max()), what="rows gx")
+    # (3) the weight gradient is additive over a split of the batch and linear in gy
+    h = B // 2
+    _, gwa = qris_b200.qnn_backward_raw(circ, xd[:h].contiguous(), wd, gd[:h].contiguous(), need_gx=False)
+    _, gwb = qris_b200.qnn_backward_raw(circ, xd[h:].contiguous(), wd, gd[h:].contiguous(), need_gx=False)
+    scale = float(gw.abs().max())
+    assert_close((gwa + gwb).cpu().numpy(), gw.cpu().numpy(), rel=2e-5, scale=scale, what="gw additivity")
+    _, gw2 = qris_b200.qnn_backward_raw(circ, xd, wd, (2.5 * gd).contiguous(), need_gx=False)
+    assert_close(gw2.cpu().numpy(), 2.5 * gw.cpu().numpy(), rel=2e-5, scale=2.5 * scale, what="gw linearity")
+    # (4) deterministic: the same call twice gives the same bits
+    _, gw3 = qris_b200.qnn_backward_raw(circ, xd, wd, gd, need_gx=False)
+    assert torch.equal(gw3, gw)
+    if kind == "ref":   # (5) last layer's RZ angles have identically zero gradient
+        assert gw.reshape(L, n, 2)[L - 1, :, 1].abs().max().item() <= 1e-3 * scale
+
+
+def test_error_paths():
+    circ = qris_b200.reference_circuit(4, 1)
+    L = qris_b200._lib
+    lib = L.lib()
+    h = circ.handle(0)
+    x = torch.zeros(8, 4, device="cuda"); w = torch.zeros(8, device="cuda"); y = torch.empty(8, 4, device="cuda")
+    need = lib.qnn_backward_workspace_bytes(h, 8)
+    assert need > 0
+    rc = lib.qnn_backward(h, x.data_ptr(), w.data_ptr(), y.data_ptr(), None, w.data_ptr(), 8, None, 0, None)
+    assert rc == -4 and b"workspace" in lib.qnn_last_error()
+    rc = lib.qnn_forward(h, x.data_ptr(), w.data_ptr(), y.data_ptr(), 0, None, 0, None)
+    assert rc == -1
+    with pytest.raises(ValueError):
+        qris_b200.qnn_apply(circ, torch.zeros(8, 5, device="cuda"), w)
+    assert qris_b200.qnn_forward_raw(circ, torch.zeros(0, 4, device="cuda"), w).shape == (0, 4)
