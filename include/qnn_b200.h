@@ -105,6 +105,22 @@ QNN_API int qnn_forward(const qnn_circuit* c, const float* x, const float* w, fl
 QNN_API int qnn_backward(const qnn_circuit* c, const float* x, const float* w, const float* gy, float* gx,
                  float* gw, int64_t B, void* workspace, size_t workspace_bytes, void* cuda_stream);
 
+/* No counterpart in the reference.  Same result as qnn_backward, for callers that cannot supply a
+ * workspace because they may not allocate device memory once running: real-time loops (a per-slot
+ * channel-estimation service) where cudaMalloc's device-wide synchronisation and unbounded latency
+ * are not acceptable, processes whose HBM is owned in full by another pool so that cudaMalloc
+ * would fail, and C / FFI hosts with no caching allocator to borrow from.  The scratch is a fixed
+ * array of QNN_STATIC_SCRATCH_BYTES inside the library image (held by every GPU that loads the
+ * library, until exit); requests that need more are refused with QNN_ERR_WORKSPACE and a message.
+ * The call allocates nothing.  Its first call on each device looks up the array's device address,
+ * so make that first call before any stream capture begins.  All calls share the one array, which
+ * keeps the previous call's contents: calls that can overlap on the GPU race -- keep them on one
+ * stream or order them.  (Nothing in it needs clearing between calls.) */
+#define QNN_STATIC_SCRATCH_BYTES (4u << 20)
+QNN_API size_t qnn_static_scratch_bytes(void);
+QNN_API int qnn_backward_static(const qnn_circuit* c, const float* x, const float* w, const float* gy,
+                                float* gx, float* gw, int64_t B, void* cuda_stream);
+
 /* QuantumNAT post-measurement pipeline (north_star; absent from the reference -- SURVEY.md 5.9):
  *   yh = (y - mean_b y) * rsqrt(var_b y + eps)   (unbiased variance; skipped if !normalise)
  *   yn = yh + sigma * noise                      (noise may be NULL -> no noise)

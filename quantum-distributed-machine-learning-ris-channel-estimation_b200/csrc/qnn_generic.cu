@@ -10,6 +10,7 @@
 // in qnn_vm.cu take over for the shapes they support.
 #include <algorithm>
 #include <cstdio>
+#include <mutex>
 
 #include "qnn_gates.cuh"
 
@@ -493,4 +494,75 @@ int generic_backward(const qnn_circuit* c, const GenericPlan& p, const float* x,
     QNN_CUDA_CHECK(cudaGetLastError());
   }
   return QNN_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// qnn_backward_static: the adjoint backward for callers that cannot hand over scratch memory.
+//
+// Who that is: a per-slot channel-estimation loop in a base-station PHY, or any real-time service,
+// sizes all of its device memory at start-up and then forbids allocation, because cudaMalloc may
+// synchronise the whole device and takes an unbounded time; a process whose HBM has been handed in
+// full to another owner's pool (an inference server, a framework arena) would simply get
+// out-of-memory from cudaMalloc; and a plain C or FFI caller has no caching allocator to borrow a
+// workspace from.  For them the scratch that qnn_backward takes from its `workspace` argument (gate
+// coefficient table, per-group gradient partials, and for n >= 14 the state vectors) lives here, in
+// one array that is part of the library image: every GPU that loads libqnn_b200.so carries
+// QNN_STATIC_SCRATCH_BYTES of it until the process exits.
+//
+// In host code `g_static_scratch` is only a handle for the symbol, not a device address, so the
+// address is looked up once per device with cudaGetSymbolAddress (that device current) and cached.
+// The lookup happens on the first call on each device: make that call before starting any stream
+// capture.  All calls share the one array and it keeps whatever the previous call left, so two calls
+// whose kernels can overlap on the GPU (different streams, or threads, without ordering) race; issue
+// them on one stream or order them yourself.  Nothing in the array has to start at zero: the kernels
+// write every coefficient row, every partial and every amplitude they later read.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[QNN_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void* g_static_ptr[kMaxDevices] = {nullptr};
+std::mutex g_static_mu;
+
+int static_scratch_for_current_device(void** out) {
+  int dev = -1;
+  QNN_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) {
+    qnn_set_error("qnn_backward_static: device ordinal %d outside [0, %d)", dev, kMaxDevices);
+    return QNN_ERR_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (g_static_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    QNN_CUDA_CHECK(cudaGetSymbolAddress(&p, g_static_scratch));
+    g_static_ptr[dev] = p;
+  }
+  *out = g_static_ptr[dev];
+  return QNN_OK;
+}
+}  // namespace
+
+extern "C" size_t qnn_static_scratch_bytes(void) { return QNN_STATIC_SCRATCH_BYTES; }
+
+extern "C" int qnn_backward_static(const qnn_circuit* c, const float* x, const float* w, const float* gy,
+                                   float* gx, float* gw, int64_t B, void* cuda_stream) {
+  if (!c) { qnn_set_error("qnn_backward_static: circuit is NULL"); return QNN_ERR_INVALID; }
+  if (B <= 0) { qnn_set_error("qnn_backward_static: B=%lld must be positive", (long long)B); return QNN_ERR_INVALID; }
+  if ((!x && c->n_inputs > 0) || (!w && c->n_weights > 0) || !gy || (!gw && c->n_weights > 0)) {
+    qnn_set_error("qnn_backward_static: NULL x, w, gy or gw");
+    return QNN_ERR_INVALID;
+  }
+  GenericPlan p;
+  generic_plan(c, B, &p);
+  const size_t need = p.ws_coef + p.ws_state_bwd + p.ws_partial;
+  if (need > QNN_STATIC_SCRATCH_BYTES) {
+    qnn_set_error("qnn_backward_static: this circuit and batch need %zu bytes of scratch but the built-in "
+                  "array holds %zu (QNN_STATIC_SCRATCH_BYTES); use qnn_backward with a caller workspace, "
+                  "or a smaller circuit", need, (size_t)QNN_STATIC_SCRATCH_BYTES);
+    return QNN_ERR_WORKSPACE;
+  }
+  void* scratch = nullptr;
+  int rc = static_scratch_for_current_device(&scratch);
+  if (rc != QNN_OK) return rc;
+  return generic_backward(c, p, x, w, gy, gx, gw, B, scratch, static_cast<cudaStream_t>(cuda_stream));
 }
