@@ -81,6 +81,10 @@ QNN_API void qnn_circuit_destroy(qnn_circuit* c);
 QNN_API int32_t qnn_circuit_n_qubits(const qnn_circuit* c);
 QNN_API int32_t qnn_circuit_n_inputs(const qnn_circuit* c);
 QNN_API int32_t qnn_circuit_n_weights(const qnn_circuit* c);
+/* JSON description of the register-resident program the circuit was lowered to (micro-ops, merged
+ * diagonals, exchanges, gradient slots), or {"ok": false, "why_not": ...} when only the generic kernels
+ * apply.  Returns the buffer size needed (including the terminator); works without a CUDA device. */
+QNN_API size_t qnn_circuit_describe(const qnn_circuit* c, char* buf, size_t len);
 /* Name of the kernel family a call with batch B would use ("generic-warp", "generic-cta", ...). */
 QNN_API const char* qnn_circuit_plan(const qnn_circuit* c, int64_t B);
 /* Number of kernel launches one qnn_forward / qnn_backward call enqueues (for launch accounting). */

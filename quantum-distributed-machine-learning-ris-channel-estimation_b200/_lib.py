@@ -42,6 +42,7 @@ SIGNATURES = {
     "qnn_circuit_n_qubits": (_i32, [_vp]),
     "qnn_circuit_n_inputs": (_i32, [_vp]),
     "qnn_circuit_n_weights": (_i32, [_vp]),
+    "qnn_circuit_describe": (_sz, [_vp, C.c_char_p, _sz]),
     "qnn_circuit_plan": (C.c_char_p, [_vp, _i64]),
     "qnn_forward_launches": (_i32, [_vp, _i64]),
     "qnn_backward_launches": (_i32, [_vp, _i64]),

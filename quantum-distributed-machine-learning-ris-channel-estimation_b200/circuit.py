@@ -79,6 +79,27 @@ class Circuit:
             self._handles[device_index] = h
         return h
 
+    def describe(self) -> dict:
+        """The register-resident program this circuit lowers to (``qnn_circuit_describe``), as a dict.
+        Works without a CUDA device (a host-only handle is created and destroyed)."""
+        import json
+        lib = _lib.lib()
+        if self._handles:
+            h, own = next(iter(self._handles.values())), False
+        else:
+            h, own = C.c_void_p(), True
+            _lib.check(lib.qnn_circuit_create(self.c_ops(), len(self.ops), self.n_qubits, self.n_inputs,
+                                              self.n_weights, _lib.ENCODER[self.encoder], C.byref(h)),
+                       "qnn_circuit_create")
+        try:
+            need = lib.qnn_circuit_describe(h, None, 0)
+            buf = C.create_string_buffer(need)
+            lib.qnn_circuit_describe(h, buf, need)
+            return json.loads(buf.value.decode())
+        finally:
+            if own:
+                lib.qnn_circuit_destroy(h)
+
     def __del__(self):
         try:
             for h in self._handles.values():

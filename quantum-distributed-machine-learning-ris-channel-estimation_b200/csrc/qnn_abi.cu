@@ -1,10 +1,13 @@
 // C ABI of libqnn_b200.so (include/qnn_b200.h): circuit lowering and kernel dispatch.
+#include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
 #include "qnn_internal.h"
+#include "qnn_vm.h"
 
 static thread_local char g_err[512] = "";
 
@@ -105,8 +108,18 @@ extern "C" int qnn_circuit_create(const qnn_op* ops, int32_t n_ops, int32_t n_qu
   { std::vector<int32_t> fill(ptr.begin(), ptr.end() - 1);
     for (int s = 0; s < c->n_slots; ++s) if (c->slot_w[s] >= 0) idx[fill[c->slot_w[s]]++] = s; }
 
+  c->vm = new (std::nothrow) vm::Program();
+  if (c->vm) vm::compile(c, c->vm);
+
   cudaError_t e = cudaGetDevice(&c->device);
-  if (e != cudaSuccess) { qnn_set_error("cudaGetDevice failed: %s (is a CUDA device present?)", cudaGetErrorString(e)); delete c; return QNN_ERR_CUDA; }
+  if (e != cudaSuccess) {
+    // No CUDA device: keep the lowered circuit for introspection (qnn_circuit_describe); every compute
+    // call on it reports QNN_ERR_CUDA.  There is no CPU execution path.
+    (void)cudaGetLastError();
+    c->device = -1;
+    *out = c;
+    return QNN_OK;
+  }
   auto upload = [&](void** dptr, const void* src, size_t bytes) -> cudaError_t {
     cudaError_t err = cudaMalloc(dptr, bytes ? bytes : 16);
     if (err != cudaSuccess) return err;
@@ -119,6 +132,12 @@ extern "C" int qnn_circuit_create(const qnn_op* ops, int32_t n_ops, int32_t n_qu
     qnn_circuit_destroy(c);
     return QNN_ERR_CUDA;
   }
+  if (c->vm && c->vm->ok) {
+    int rc = vm::upload(c->vm, n_weights);
+    if (rc != QNN_OK) { qnn_circuit_destroy(c); return rc; }
+    const char* off = getenv("QNN_DISABLE_VM");
+    c->use_vm = !(off && off[0] == '1');
+  }
   *out = c;
   return QNN_OK;
 }
@@ -128,6 +147,7 @@ extern "C" void qnn_circuit_destroy(qnn_circuit* c) {
   if (c->d_ops) cudaFree(c->d_ops);
   if (c->d_slot_ptr) cudaFree(c->d_slot_ptr);
   if (c->d_slot_idx) cudaFree(c->d_slot_idx);
+  if (c->vm) { vm::release(c->vm); delete c->vm; }
   delete c;
 }
 
@@ -135,31 +155,58 @@ extern "C" int32_t qnn_circuit_n_qubits(const qnn_circuit* c) { return c ? c->n_
 extern "C" int32_t qnn_circuit_n_inputs(const qnn_circuit* c) { return c ? c->n_inputs : -1; }
 extern "C" int32_t qnn_circuit_n_weights(const qnn_circuit* c) { return c ? c->n_weights : -1; }
 
+extern "C" size_t qnn_circuit_describe(const qnn_circuit* c, char* buf, size_t len) {
+  if (!c || !c->vm) return 0;
+  const std::string s = vm::describe(*c->vm);
+  if (buf && len > 0) {
+    const size_t k = std::min(len - 1, s.size());
+    memcpy(buf, s.data(), k);
+    buf[k] = 0;
+  }
+  return s.size() + 1;
+}
+
+// Which kernel family serves (circuit, B): the register-resident VM when the circuit lowered to it
+// and its tables fit in shared memory, otherwise the generic interpreter.
+static bool vm_plan(const qnn_circuit* c, int64_t B, vm::Plan* pl) {
+  return c->use_vm && c->vm && vm::plan(c, *c->vm, B, pl);
+}
+
 extern "C" const char* qnn_circuit_plan(const qnn_circuit* c, int64_t B) {
   if (!c) return "";
+  vm::Plan vp;
+  if (vm_plan(c, B, &vp)) { c->plan_name = "vm-register"; return c->plan_name.c_str(); }
   GenericPlan p;
   generic_plan(c, B, &p);
   c->plan_name = p.name;
   return c->plan_name.c_str();
 }
 
-extern "C" int32_t qnn_forward_launches(const qnn_circuit* c, int64_t) {
+extern "C" int32_t qnn_forward_launches(const qnn_circuit* c, int64_t B) {
   if (!c) return 0;
+  vm::Plan vp;
+  if (vm_plan(c, B, &vp)) return 2;
   return 1 + (c->n_coef > 0 ? 1 : 0);
 }
-extern "C" int32_t qnn_backward_launches(const qnn_circuit* c, int64_t) {
+extern "C" int32_t qnn_backward_launches(const qnn_circuit* c, int64_t B) {
   if (!c) return 0;
+  vm::Plan vp;
+  if (vm_plan(c, B, &vp)) return 2 + (c->n_weights > 0 ? 1 : 0);
   return 1 + (c->n_coef > 0 ? 1 : 0) + (c->n_weights > 0 ? 1 : 0);
 }
 
 extern "C" size_t qnn_forward_workspace_bytes(const qnn_circuit* c, int64_t B) {
   if (!c || B <= 0) return 0;
+  vm::Plan vp;
+  if (vm_plan(c, B, &vp)) return vp.ws_coef + vp.ws_diag;
   GenericPlan p;
   generic_plan(c, B, &p);
   return p.ws_coef + p.ws_state_fwd;
 }
 extern "C" size_t qnn_backward_workspace_bytes(const qnn_circuit* c, int64_t B) {
   if (!c || B <= 0) return 0;
+  vm::Plan vp;
+  if (vm_plan(c, B, &vp)) return vp.ws_coef + vp.ws_diag + vp.ws_partial;
   GenericPlan p;
   generic_plan(c, B, &p);
   return p.ws_coef + p.ws_state_bwd + p.ws_partial;
@@ -168,6 +215,7 @@ extern "C" size_t qnn_backward_workspace_bytes(const qnn_circuit* c, int64_t B) 
 static int check_common(const char* fn, const qnn_circuit* c, const float* x, const float* w, int64_t B) {
   if (!c) { qnn_set_error("%s: circuit is NULL", fn); return QNN_ERR_INVALID; }
   if (B <= 0) { qnn_set_error("%s: B=%lld must be positive", fn, (long long)B); return QNN_ERR_INVALID; }
+  if (c->device < 0) { qnn_set_error("%s: the circuit was created without a CUDA device; there is no CPU path", fn); return QNN_ERR_CUDA; }
   if (!x && c->n_inputs > 0) { qnn_set_error("%s: x is NULL", fn); return QNN_ERR_INVALID; }
   if (!w && c->n_weights > 0) { qnn_set_error("%s: w is NULL", fn); return QNN_ERR_INVALID; }
   return QNN_OK;
@@ -178,13 +226,15 @@ extern "C" int qnn_forward(const qnn_circuit* c, const float* x, const float* w,
   int rc = check_common("qnn_forward", c, x, w, B);
   if (rc) return rc;
   if (!y) { qnn_set_error("qnn_forward: y is NULL"); return QNN_ERR_INVALID; }
-  GenericPlan p;
-  generic_plan(c, B, &p);
-  const size_t need = p.ws_coef + p.ws_state_fwd;
+  const size_t need = qnn_forward_workspace_bytes(c, B);
   if (need > 0 && (!workspace || workspace_bytes < need)) {
     qnn_set_error("qnn_forward: workspace of %zu bytes needed, %zu given", need, workspace ? workspace_bytes : (size_t)0);
     return QNN_ERR_WORKSPACE;
   }
+  vm::Plan vp;
+  if (vm_plan(c, B, &vp)) return vm::forward(c, *c->vm, vp, x, w, y, B, workspace, static_cast<cudaStream_t>(cuda_stream));
+  GenericPlan p;
+  generic_plan(c, B, &p);
   return generic_forward(c, p, x, w, y, B, workspace, static_cast<cudaStream_t>(cuda_stream));
 }
 
@@ -195,12 +245,14 @@ extern "C" int qnn_backward(const qnn_circuit* c, const float* x, const float* w
   if (rc) return rc;
   if (!gy) { qnn_set_error("qnn_backward: gy is NULL"); return QNN_ERR_INVALID; }
   if (!gw && c->n_weights > 0) { qnn_set_error("qnn_backward: gw is NULL"); return QNN_ERR_INVALID; }
-  GenericPlan p;
-  generic_plan(c, B, &p);
-  const size_t need = p.ws_coef + p.ws_state_bwd + p.ws_partial;
+  const size_t need = qnn_backward_workspace_bytes(c, B);
   if (!workspace || workspace_bytes < need) {
     qnn_set_error("qnn_backward: workspace of %zu bytes needed, %zu given", need, workspace ? workspace_bytes : (size_t)0);
     return QNN_ERR_WORKSPACE;
   }
+  vm::Plan vp;
+  if (vm_plan(c, B, &vp)) return vm::backward(c, *c->vm, vp, x, w, gy, gx, gw, B, workspace, static_cast<cudaStream_t>(cuda_stream));
+  GenericPlan p;
+  generic_plan(c, B, &p);
   return generic_backward(c, p, x, w, gy, gx, gw, B, workspace, static_cast<cudaStream_t>(cuda_stream));
 }

@@ -23,6 +23,8 @@ struct DevOp {
   int32_t pad;
 };
 
+namespace vm { struct Program; }
+
 struct qnn_circuit {
   int32_t n_qubits = 0, n_inputs = 0, n_weights = 0, encoder = 0;
   std::vector<qnn_op> ops;        // as given
@@ -36,6 +38,8 @@ struct qnn_circuit {
   int32_t* d_slot_ptr = nullptr;  // CSR weight -> slots
   int32_t* d_slot_idx = nullptr;
   mutable std::string plan_name;
+  vm::Program* vm = nullptr;      // register-resident program (qnn_vm.h); vm->ok says whether it applies
+  bool use_vm = false;            // vm->ok and not disabled by QNN_DISABLE_VM=1 (tests of the generic family)
 };
 
 void qnn_set_error(const char* fmt, ...);

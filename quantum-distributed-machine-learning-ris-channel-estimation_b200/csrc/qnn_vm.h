@@ -1,0 +1,109 @@
+// Register-resident statevector VM: program format shared by the host compiler (qnn_vm_compile.cpp)
+// and the kernels (qnn_vm.cu).
+//
+// Geometry: every thread keeps 2^R = 32 complex amplitudes of one sample in registers (R = 5 "register
+// bits"); 2^TB lanes of a warp share a sample (TB = n - 5 "lane bits", n = 5..10), so a warp carries
+// 32 / 2^TB samples and always 1024 amplitudes.  A *layout* says which logical wire sits on which
+// physical bit; gates act only on register bits, and an EXCHANGE micro-op re-lays the state out
+// through a warp-private shared-memory buffer with GF(2)-linear, bank-conflict-free addressing.
+// CNOTs cost nothing: they update the layout matrix and are materialised by the next exchange.
+// RZ / CZ (and the RZ factors of U3 = RZ RY RZ) are merged into DIAG micro-ops.
+#pragma once
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "qnn_internal.h"
+
+namespace vm {
+
+constexpr int kR = 5;                  // register bits
+constexpr int kAmps = 1 << kR;         // amplitudes per thread
+constexpr int kWarpAmps = 1024;        // amplitudes per warp (any TB)
+constexpr int kMinQubits = 5, kMaxQubits = 10;
+
+enum MopKind : int32_t {
+  MOP_END = 0,
+  MOP_G1_REAL = 1,    // real rotation [[c,-s],[s,c]] on register bit a; coef row idx; acc (1 float)
+  MOP_G1_REAL_X = 2,  // same, angle = x[b, idx] (per sample); gradient goes to gx
+  MOP_G1_GEN = 3,     // general complex 2x2 on register bit a; coef row idx; acc (8 floats: T)
+  MOP_CG1_L = 4,      // controlled 2x2: target register bit a, control register bit b
+  MOP_CG1_P = 5,      // controlled 2x2: target register bit a, control = parity(lane_in_sample & aux)
+  MOP_DIAG = 6,       // multiply by diagonal table idx ([j][lane], 1024 entries); desc aux
+  MOP_DIAG_REG = 7,   // diagonal that depends on register bits only (32-entry table idx); desc aux
+  MOP_XCHG = 8,       // exchange idx
+};
+
+struct MicroOp {       // 32 bytes
+  int32_t kind, a, b, idx, acc, aux, pad0, pad1;
+};
+
+struct DiagTerm {      // one factor of a diagonal: RZ(angle) on a physical bit, or CZ on two bits
+  int32_t kind;        // 0: RZ, 1: CZ
+  int32_t src;         // RZ angle source (qnn_op convention), QNN_SRC_CONST -> value
+  float value;
+  int32_t bit0, bit1;  // physical bit(s), in the layout current when the diagonal is applied
+};
+
+struct DiagDesc {      // per DIAG / DIAG_REG micro-op
+  int32_t first_term, n_terms;
+  int32_t table;       // DIAG: offset (in float2) into the big-table area; DIAG_REG: into the small one
+  int32_t is_reg;
+  int32_t acc_reg[kR];   // accumulator index receiving sum_p z_bit(p) Im(conj(lam_p) psi_p), or -1
+  int32_t acc_lane[5];   // same for lane bits
+};
+
+struct Exchange {      // byte offsets into the warp's 8 KB buffer; address = base[lane] ^ off[j]
+  uint32_t wbase[32], woff[32], rbase[32], roff[32];
+};
+
+struct GradSlot {      // how one weight-sourced angle's gradient is obtained from the accumulators
+  int32_t weight;      // index into gw
+  int32_t kind;        // 0: direct (value = acc[a]);  1: 2 Re sum G_k T (acc base a, coef row c, angle k)
+  int32_t acc, coef, angle;
+};
+
+struct Program {
+  bool ok = false;
+  std::string why_not;           // when !ok: why the VM does not take this circuit (generic path used)
+  int n = 0, tb = 0;
+  std::vector<MicroOp> ops;      // forward order, MOP_END-terminated
+  std::vector<DevOp> coef_ops;   // recipes for k_prep_coef (mode 1), one per coefficient row
+  std::vector<DiagTerm> terms;
+  std::vector<DiagDesc> diags;
+  std::vector<Exchange> exchanges;
+  std::vector<GradSlot> slots;
+  int n_acc = 0;                 // floats of gradient accumulators
+  int n_big_tables = 0, n_small_tables = 0;
+  int final_bit_of_wire[16];     // physical bit holding each wire at measurement (clean layout)
+  int initial_bit_of_wire[16];
+  // device copies
+  MicroOp* d_ops = nullptr;
+  DevOp* d_coef_ops = nullptr;
+  DiagTerm* d_terms = nullptr;
+  DiagDesc* d_diags = nullptr;
+  Exchange* d_exchanges = nullptr;
+  GradSlot* d_slots = nullptr;
+  int32_t* d_slot_ptr = nullptr;  // CSR weight -> slots
+  int32_t* d_slot_idx = nullptr;
+};
+
+// Lower a validated circuit.  Never fails hard: sets ok=false + why_not when out of the VM's scope.
+void compile(const qnn_circuit* c, Program* out);
+std::string describe(const Program& p);   // JSON, for tests and introspection
+
+struct Plan {
+  int threads, grid, warps_per_cta;
+  size_t smem_fwd, smem_bwd;
+  size_t ws_coef, ws_diag, ws_partial;   // bytes (each 256-aligned)
+};
+bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out);
+int upload(Program* p, int n_weights);
+void release(Program* p);
+int forward(const qnn_circuit* c, const Program& p, const Plan& pl, const float* x, const float* w, float* y,
+            int64_t B, void* ws, cudaStream_t st);
+int backward(const qnn_circuit* c, const Program& p, const Plan& pl, const float* x, const float* w,
+             const float* gy, float* gx, float* gw, int64_t B, void* ws, cudaStream_t st);
+
+}  // namespace vm

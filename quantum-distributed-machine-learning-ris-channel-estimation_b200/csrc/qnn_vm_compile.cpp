@@ -1,0 +1,539 @@
+// Host-side compiler of the register-resident statevector VM (see qnn_vm.h).
+//
+// Input: the validated gate list of a qnn_circuit.  Output: a linear micro-op program plus the tables
+// the kernels need.  Three ideas carry the performance:
+//   1. list scheduling over the gate DAG so that as many gates as possible run while their target wire
+//      sits on a register bit; when nothing more can run, ONE exchange brings the next wires in;
+//   2. CNOTs are free: they only update the GF(2) layout (rowmask[wire] ^= rowmask[control]); the next
+//      exchange materialises the accumulated permutation in its addressing;
+//   3. diagonal gates (RZ, CZ, and the two RZ factors of U3 = e^{ia} RZ(phi) RY(theta) RZ(lambda)) are
+//      collected and applied as one table multiply.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <sstream>
+
+#include "qnn_vm.h"
+
+namespace vm {
+namespace {
+
+enum ItemKind { IT_REAL, IT_GEN, IT_RZ, IT_CZ, IT_CNOT, IT_CGEN };
+
+struct Item {
+  ItemKind kind;
+  int w0, w1;          // w0: target of 1q / control of 2q;  w1: target of 2q
+  int gate;            // qnn_gate for coefficient recipes (IT_GEN: RX; IT_CGEN: CU3)
+  int32_t src[3];
+  float value[3];
+  bool done = false;
+};
+
+inline int ctz(uint32_t v) { return __builtin_ctz(v); }
+inline bool is_unit(uint32_t v) { return v != 0 && (v & (v - 1)) == 0; }
+
+struct Lcg {
+  uint64_t s;
+  uint32_t next() { s = s * 6364136223846793005ULL + 1442695040888963407ULL; return (uint32_t)(s >> 33); }
+};
+
+// rank of a set of `cnt` vectors of `bits` bits == cnt ?
+bool independent(const uint32_t* v, int cnt) {
+  uint32_t basis[16];
+  int nb = 0;
+  for (int i = 0; i < cnt; ++i) {
+    uint32_t x = v[i];
+    for (int b = 0; b < nb; ++b) x = std::min(x, x ^ basis[b]);
+    if (!x) return false;
+    basis[nb++] = x;
+  }
+  return true;
+}
+
+// Solve M p = e_w for every wire w, M given by rows rowmask[w] (bit b of rowmask = column b).
+bool invert(const uint32_t* rowmask, int n, uint32_t* inv_col) {
+  // Augmented elimination on rows: [rowmask | identity(wire)]
+  uint32_t a[16], id[16];
+  for (int i = 0; i < n; ++i) { a[i] = rowmask[i]; id[i] = 1u << i; }
+  int piv_row_of_col[16];
+  int r = 0;
+  for (int col = 0; col < n; ++col) {
+    int p = -1;
+    for (int i = r; i < n; ++i) if ((a[i] >> col) & 1u) { p = i; break; }
+    if (p < 0) return false;
+    std::swap(a[p], a[r]); std::swap(id[p], id[r]);
+    for (int i = 0; i < n; ++i) if (i != r && ((a[i] >> col) & 1u)) { a[i] ^= a[r]; id[i] ^= id[r]; }
+    piv_row_of_col[col] = r;
+    ++r;
+  }
+  // Now a[piv_row_of_col[col]] == 1<<col and id[...] = combination of wires: p_col = parity(id & k).
+  // inv_col[w] = mask of physical bits col with (id[row(col)] >> w) & 1.
+  for (int w = 0; w < n; ++w) {
+    uint32_t m = 0;
+    for (int col = 0; col < n; ++col) if ((id[piv_row_of_col[col]] >> w) & 1u) m |= 1u << col;
+    inv_col[w] = m;
+  }
+  return true;
+}
+
+struct Builder {
+  const qnn_circuit* c;
+  Program* P;
+  int n, tb;
+  int policy = 0;   // how "apply the pending diagonal" and "exchange" are ordered when both are possible
+  std::vector<Item> items;
+  uint32_t rowmask[16];
+  struct Pending { int item; };
+  std::vector<int> pending;          // item indices of RZ / CZ terms waiting for a flush
+  std::vector<std::vector<int>> by_wire;
+  std::vector<size_t> head;          // per wire: index into by_wire[w] of the first not-done item
+
+  bool lower_items() {
+    for (size_t i = 0; i < c->ops.size(); ++i) {
+      const qnn_op& o = c->ops[i];
+      auto x_src = [](int32_t s) { return s < 0 && s != QNN_SRC_CONST; };
+      Item it{};
+      for (int k = 0; k < 3; ++k) { it.src[k] = QNN_SRC_CONST; it.value[k] = 0.f; }
+      switch (o.kind) {
+        case QNN_RY:
+          it.kind = IT_REAL; it.w0 = o.wire0; it.w1 = -1; it.gate = QNN_RY; it.src[0] = o.src[0]; it.value[0] = o.value[0];
+          items.push_back(it);
+          break;
+        case QNN_RX:
+          if (x_src(o.src[0])) { P->why_not = "RX with an input-sourced angle"; return false; }
+          it.kind = IT_GEN; it.w0 = o.wire0; it.w1 = -1; it.gate = QNN_RX; it.src[0] = o.src[0]; it.value[0] = o.value[0];
+          items.push_back(it);
+          break;
+        case QNN_RZ:
+          if (x_src(o.src[0])) { P->why_not = "RZ with an input-sourced angle"; return false; }
+          it.kind = IT_RZ; it.w0 = o.wire0; it.w1 = -1; it.gate = QNN_RZ; it.src[0] = o.src[0]; it.value[0] = o.value[0];
+          items.push_back(it);
+          break;
+        case QNN_U3: {
+          for (int k = 0; k < 3; ++k) if (x_src(o.src[k])) { P->why_not = "U3 with an input-sourced angle"; return false; }
+          // U3(t,p,l) = e^{i(p+l)/2} RZ(p) RY(t) RZ(l); the global phase drops out of <Z> and of all gradients
+          Item a = it; a.kind = IT_RZ; a.w0 = o.wire0; a.w1 = -1; a.gate = QNN_RZ; a.src[0] = o.src[2]; a.value[0] = o.value[2];
+          Item b = it; b.kind = IT_REAL; b.w0 = o.wire0; b.w1 = -1; b.gate = QNN_RY; b.src[0] = o.src[0]; b.value[0] = o.value[0];
+          Item d = it; d.kind = IT_RZ; d.w0 = o.wire0; d.w1 = -1; d.gate = QNN_RZ; d.src[0] = o.src[1]; d.value[0] = o.value[1];
+          items.push_back(a); items.push_back(b); items.push_back(d);
+          break;
+        }
+        case QNN_CNOT:
+          it.kind = IT_CNOT; it.w0 = o.wire0; it.w1 = o.wire1; it.gate = QNN_CNOT;
+          items.push_back(it);
+          break;
+        case QNN_CZ:
+          it.kind = IT_CZ; it.w0 = o.wire0; it.w1 = o.wire1; it.gate = QNN_CZ;
+          items.push_back(it);
+          break;
+        case QNN_CU3:
+          for (int k = 0; k < 3; ++k) {
+            if (x_src(o.src[k])) { P->why_not = "CU3 with an input-sourced angle"; return false; }
+            it.src[k] = o.src[k]; it.value[k] = o.value[k];
+          }
+          it.kind = IT_CGEN; it.w0 = o.wire0; it.w1 = o.wire1; it.gate = QNN_CU3;
+          items.push_back(it);
+          break;
+        default:
+          P->why_not = "unknown gate";
+          return false;
+      }
+    }
+    by_wire.assign(n, {});
+    for (size_t i = 0; i < items.size(); ++i) {
+      by_wire[items[i].w0].push_back((int)i);
+      if (items[i].w1 >= 0) by_wire[items[i].w1].push_back((int)i);
+    }
+    head.assign(n, 0);
+    return true;
+  }
+
+  bool ready(int i) const {
+    const Item& it = items[i];
+    auto first = [&](int w) { return head[w] < by_wire[w].size() ? by_wire[w][head[w]] : -1; };
+    if (first(it.w0) != i) return false;
+    if (it.w1 >= 0 && first(it.w1) != i) return false;
+    return true;
+  }
+  void mark_done(int i) {
+    items[i].done = true;
+    for (int w : {items[i].w0, items[i].w1}) {
+      if (w < 0) continue;
+      while (head[w] < by_wire[w].size() && items[by_wire[w][head[w]]].done) ++head[w];
+    }
+  }
+
+  bool row_unit(int w) const { return is_unit(rowmask[w]); }
+  bool clean(int w) const {   // the wire's physical bit carries this wire and nothing else
+    if (!is_unit(rowmask[w])) return false;
+    for (int v = 0; v < n; ++v) if (v != w && (rowmask[v] & rowmask[w])) return false;
+    return true;
+  }
+  int bit_of(int w) const { return ctz(rowmask[w]); }
+  bool pending_on(int w) const {
+    for (int i : pending) if (items[i].w0 == w || items[i].w1 == w) return true;
+    return false;
+  }
+
+  int new_coef_row(int gate, const int32_t* src, const float* value, int nang) {
+    DevOp d{};
+    d.kind = gate; d.tpos = 0; d.cpos = -1; d.mode = 1; d.nang = nang; d.slot = -1;
+    for (int k = 0; k < 3; ++k) { d.src[k] = src[k]; d.value[k] = value[k]; }
+    d.coef = (int)P->coef_ops.size();
+    P->coef_ops.push_back(d);
+    return d.coef;
+  }
+
+  void flush_diag() {
+    if (pending.empty()) return;
+    DiagDesc D{};
+    D.first_term = (int)P->terms.size();
+    for (int r = 0; r < kR; ++r) D.acc_reg[r] = -1;
+    for (int l = 0; l < 5; ++l) D.acc_lane[l] = -1;
+    bool reg_only = true;
+    for (int i : pending) {
+      const Item& it = items[i];
+      DiagTerm t{};
+      t.kind = it.kind == IT_CZ ? 1 : 0;
+      t.src = it.src[0]; t.value = it.value[0];
+      t.bit0 = bit_of(it.w0);
+      t.bit1 = it.kind == IT_CZ ? bit_of(it.w1) : -1;
+      if (t.bit0 >= kR || t.bit1 >= kR) reg_only = false;
+      if (t.kind == 0 && t.src >= 0) {
+        int32_t& a = t.bit0 < kR ? D.acc_reg[t.bit0] : D.acc_lane[t.bit0 - kR];
+        if (a < 0) a = P->n_acc++;
+        P->slots.push_back(GradSlot{t.src, 0, a, -1, 0});
+      }
+      P->terms.push_back(t);
+    }
+    D.n_terms = (int)pending.size();
+    D.is_reg = reg_only ? 1 : 0;
+    D.table = reg_only ? P->n_small_tables++ : P->n_big_tables++;
+    MicroOp m{};
+    m.kind = reg_only ? MOP_DIAG_REG : MOP_DIAG;
+    m.idx = D.table; m.aux = (int)P->diags.size(); m.acc = -1;
+    P->diags.push_back(D);
+    P->ops.push_back(m);
+    pending.clear();
+  }
+
+  enum Status { ST_OK, ST_NEEDS_FLUSH, ST_BLOCKED };
+  // Can item i run in the current layout?  ST_NEEDS_FLUSH: yes, once the pending diagonal is applied.
+  Status classify(int i) const {
+    const Item& it = items[i];
+    switch (it.kind) {
+      case IT_RZ: return row_unit(it.w0) ? ST_OK : ST_BLOCKED;
+      case IT_CZ: return (row_unit(it.w0) && row_unit(it.w1)) ? ST_OK : ST_BLOCKED;
+      case IT_CNOT: return pending_on(it.w1) ? ST_NEEDS_FLUSH : ST_OK;
+      case IT_REAL:
+      case IT_GEN:
+        if (!clean(it.w0) || bit_of(it.w0) >= kR) return ST_BLOCKED;
+        return pending_on(it.w0) ? ST_NEEDS_FLUSH : ST_OK;
+      case IT_CGEN:
+        if (!clean(it.w1) || bit_of(it.w1) >= kR || !row_unit(it.w0)) return ST_BLOCKED;
+        return pending_on(it.w1) ? ST_NEEDS_FLUSH : ST_OK;
+    }
+    return ST_BLOCKED;
+  }
+
+  // Execute item i in the current layout (flushing the pending diagonal if it must).
+  bool try_exec(int i) {
+    Item& it = items[i];
+    switch (it.kind) {
+      case IT_RZ:
+        if (!row_unit(it.w0)) return false;
+        pending.push_back(i);
+        return true;
+      case IT_CZ:
+        if (!row_unit(it.w0) || !row_unit(it.w1)) return false;
+        pending.push_back(i);
+        return true;
+      case IT_CNOT:
+        if (pending_on(it.w1)) flush_diag();
+        rowmask[it.w1] ^= rowmask[it.w0];
+        return true;
+      case IT_REAL:
+      case IT_GEN: {
+        if (!clean(it.w0) || bit_of(it.w0) >= kR) return false;
+        if (pending_on(it.w0)) flush_diag();
+        MicroOp m{};
+        m.a = bit_of(it.w0); m.acc = -1;
+        if (it.kind == IT_REAL) {
+          if (it.src[0] < 0 && it.src[0] != QNN_SRC_CONST) {
+            m.kind = MOP_G1_REAL_X; m.idx = -1 - it.src[0];
+          } else {
+            m.kind = MOP_G1_REAL; m.idx = new_coef_row(QNN_RY, it.src, it.value, 1);
+            if (it.src[0] >= 0) { m.acc = P->n_acc++; P->slots.push_back(GradSlot{it.src[0], 0, m.acc, -1, 0}); }
+          }
+        } else {
+          m.kind = MOP_G1_GEN; m.idx = new_coef_row(it.gate, it.src, it.value, 1);
+          if (it.src[0] >= 0) { m.acc = P->n_acc; P->n_acc += 8; P->slots.push_back(GradSlot{it.src[0], 1, m.acc, m.idx, 0}); }
+        }
+        P->ops.push_back(m);
+        return true;
+      }
+      case IT_CGEN: {
+        if (!clean(it.w1) || bit_of(it.w1) >= kR || !row_unit(it.w0)) return false;
+        if (pending_on(it.w1)) flush_diag();
+        MicroOp m{};
+        m.a = bit_of(it.w1); m.acc = -1;
+        const int cb = bit_of(it.w0);
+        if (cb < kR) { m.kind = MOP_CG1_L; m.b = cb; }
+        else { m.kind = MOP_CG1_P; m.aux = 1 << (cb - kR); }
+        m.idx = new_coef_row(QNN_CU3, it.src, it.value, 3);
+        bool any_w = false;
+        for (int k = 0; k < 3; ++k) any_w |= it.src[k] >= 0;
+        if (any_w) {
+          m.acc = P->n_acc; P->n_acc += 8;
+          for (int k = 0; k < 3; ++k) if (it.src[k] >= 0) P->slots.push_back(GradSlot{it.src[k], 1, m.acc, m.idx, k});
+        }
+        P->ops.push_back(m);
+        return true;
+      }
+    }
+    return false;
+  }
+
+  // Wires wanted on register bits next, in order of need.
+  void choose_layout(int* bit_of_wire) {
+    std::vector<int> order;
+    auto add = [&](int w) { if (w >= 0 && std::find(order.begin(), order.end(), w) == order.end()) order.push_back(w); };
+    for (size_t i = 0; i < items.size() && (int)order.size() < kR; ++i) {
+      if (items[i].done) continue;
+      if (items[i].kind == IT_REAL || items[i].kind == IT_GEN) add(items[i].w0);
+      else if (items[i].kind == IT_CGEN) add(items[i].w1);
+    }
+    for (size_t i = 0; i < items.size() && (int)order.size() < kR; ++i)
+      if (!items[i].done && items[i].kind == IT_CGEN) add(items[i].w0);
+    for (int w = 0; w < n && (int)order.size() < kR; ++w)
+      if (is_unit(rowmask[w]) && ctz(rowmask[w]) < kR) add(w);
+    for (int w = 0; w < n && (int)order.size() < kR; ++w) add(w);
+    std::vector<bool> used(n, false);
+    for (int r = 0; r < kR; ++r) { bit_of_wire[order[r]] = r; used[order[r]] = true; }
+    int b = kR;
+    for (int w = 0; w < n; ++w) if (!used[w]) bit_of_wire[w] = b++;
+  }
+
+  bool emit_exchange(const int* new_bit_of_wire) {
+    uint32_t inv_col[16];
+    if (!invert(rowmask, n, inv_col)) { P->why_not = "internal: singular layout"; return false; }
+    // acol[b']: old extended index contributed by new extended bit b'
+    uint32_t acol[10];
+    for (int w = 0; w < n; ++w) acol[new_bit_of_wire[w]] = inv_col[w];
+    for (int b = n; b < 10; ++b) acol[b] = 1u << b;      // sample-in-warp bits stay put
+    // slot map S (columns scol[e], 10-bit), bank-conflict-free for 64-bit accesses on both sides
+    Lcg rng{0x9E3779B97F4A7C15ULL + P->exchanges.size() * 7919ULL};
+    uint32_t scol[10], rcol[10];
+    for (int attempt = 0;; ++attempt) {
+      if (attempt > 100000) { P->why_not = "internal: no conflict-free exchange found"; return false; }
+      for (int e = 0; e < 10; ++e) scol[e] = rng.next() & 1023u;
+      if (!independent(scol, 10)) continue;
+      for (int b = 0; b < 10; ++b) {
+        uint32_t s = 0;
+        for (int e = 0; e < 10; ++e) if ((acol[b] >> e) & 1u) s ^= scol[e];
+        rcol[b] = s;
+      }
+      uint32_t wlow[4], rlow[4];
+      for (int i = 0; i < 4; ++i) { wlow[i] = scol[5 + i] & 15u; rlow[i] = rcol[5 + i] & 15u; }
+      if (independent(wlow, 4) && independent(rlow, 4)) break;
+    }
+    Exchange X{};
+    for (int v = 0; v < 32; ++v) {
+      uint32_t wb = 0, wo = 0, rb = 0, ro = 0;
+      for (int i = 0; i < 5; ++i) if ((v >> i) & 1) { wo ^= scol[i]; wb ^= scol[5 + i]; ro ^= rcol[i]; rb ^= rcol[5 + i]; }
+      X.wbase[v] = wb * 8; X.woff[v] = wo * 8;
+      X.rbase[v] = rb * 8; X.roff[v] = ro * 8;
+    }
+    MicroOp m{};
+    m.kind = MOP_XCHG; m.idx = (int)P->exchanges.size(); m.acc = -1;
+    P->exchanges.push_back(X);
+    P->ops.push_back(m);
+    for (int w = 0; w < n; ++w) rowmask[w] = 1u << new_bit_of_wire[w];
+    return true;
+  }
+
+  bool all_clean() const {
+    uint32_t seen = 0;
+    for (int w = 0; w < n; ++w) {
+      if (!is_unit(rowmask[w]) || (seen & rowmask[w])) return false;
+      seen |= rowmask[w];
+    }
+    return true;
+  }
+
+  bool run() {
+    n = c->n_qubits;
+    tb = n - kR;
+    P->n = n; P->tb = tb;
+    if (n < kMinQubits || n > kMaxQubits) { P->why_not = "n_qubits outside [5, 10]"; return false; }
+    if (c->encoder != QNN_ENC_NONE) { P->why_not = "amplitude encoder"; return false; }
+    if (c->n_inputs > 32) { P->why_not = "more than 32 input columns"; return false; }
+    if (!lower_items()) return false;
+    int bits[16];
+    for (int w = 0; w < n; ++w) rowmask[w] = 1u << w;   // provisional, only "unit-ness" matters here
+    choose_layout(bits);
+    for (int w = 0; w < n; ++w) { rowmask[w] = 1u << bits[w]; P->initial_bit_of_wire[w] = bits[w]; }
+    size_t remaining = items.size();
+    // One sweep over the ready items; runs those whose status is ST_OK and that `want` accepts.
+    auto sweep = [&](auto want) {
+      bool progress = false;
+      for (size_t i = 0; i < items.size(); ++i) {
+        if (items[i].done || !ready((int)i) || !want(items[i]) || classify((int)i) != ST_OK) continue;
+        if (try_exec((int)i)) { mark_done((int)i); --remaining; progress = true; }
+      }
+      return progress;
+    };
+    auto first_ready = [&](auto pred) {   // program-order index of the first ready item satisfying pred, or -1
+      for (size_t i = 0; i < items.size(); ++i)
+        if (!items[i].done && ready((int)i) && pred((int)i)) return (int)i;
+      return -1;
+    };
+    while (remaining > 0) {
+      // 1. everything that needs neither a flush nor layout bookkeeping
+      if (sweep([](const Item& it) { return it.kind != IT_CNOT; })) continue;
+      // 2. CNOTs that are free right now (they dirty the layout, so they go after the real work)
+      if (sweep([](const Item& it) { return it.kind == IT_CNOT; })) continue;
+      // 3./4. a gate that is local and clean but waits for the pending diagonal -> apply the diagonal;
+      //       a gate that waits for its wire to come onto a register bit (or to be cleaned) -> exchange.
+      //       Whichever waiting gate comes first in program order decides, so that work of the next
+      //       layer does not fragment the diagonals of this one.
+      const int f = first_ready([&](int i) { return items[i].kind != IT_CNOT && classify(i) == ST_NEEDS_FLUSH; });
+      const int b = first_ready([&](int i) { return classify(i) == ST_BLOCKED; });
+      bool flush_first = f >= 0 && (b < 0 || f < b);
+      if (f >= 0 && policy == 0) flush_first = true;               // always finish local work first
+      if (f >= 0 && policy == 2 && items[f].kind == IT_CGEN) {     // ... only for two-qubit gates whose
+        bool all_local = true;                                      //     pending terms are register-only
+        for (int i : pending) {
+          if (bit_of(items[i].w0) >= kR) all_local = false;
+          if (items[i].w1 >= 0 && bit_of(items[i].w1) >= kR) all_local = false;
+        }
+        if (all_local) flush_first = true;
+      }
+      if (flush_first) { flush_diag(); continue; }
+      if (b >= 0) {
+        choose_layout(bits);
+        if (!emit_exchange(bits)) return false;
+        continue;
+      }
+      // 5. only CNOTs whose target carries a pending diagonal term are left: apply the diagonal
+      if (!pending.empty()) { flush_diag(); continue; }
+      P->why_not = "internal: scheduler made no progress";
+      return false;
+    }
+    // trailing diagonal terms do not change <Z> and have identically zero gradient: drop them
+    pending.clear();
+    if (!all_clean()) {
+      for (int w = 0; w < n; ++w) bits[w] = -1;
+      // keep wires that are clean where they are; give the rest the free bits
+      uint32_t taken = 0;
+      for (int w = 0; w < n; ++w) if (clean(w)) { bits[w] = bit_of(w); taken |= 1u << bits[w]; }
+      for (int w = 0; w < n; ++w) if (bits[w] < 0) { int b = 0; while ((taken >> b) & 1u) ++b; bits[w] = b; taken |= 1u << b; }
+      if (!emit_exchange(bits)) return false;
+    }
+    for (int w = 0; w < n; ++w) P->final_bit_of_wire[w] = bit_of(w);
+    MicroOp e{};
+    e.kind = MOP_END; e.acc = -1;
+    P->ops.push_back(e);
+    P->ok = true;
+    return true;
+  }
+};
+
+}  // namespace
+
+// Estimated issue slots per amplitude of one forward pass (the backward pass scales alike).
+static double program_cost(const Program& p) {
+  double cost = 0;
+  for (const MicroOp& m : p.ops) {
+    switch (m.kind) {
+      case MOP_G1_REAL: case MOP_G1_REAL_X: case MOP_CG1_L: case MOP_DIAG_REG: cost += 4; break;
+      case MOP_G1_GEN: case MOP_CG1_P: cost += 8; break;
+      case MOP_DIAG: cost += 4.5; break;
+      case MOP_XCHG: cost += 4.6; break;
+      default: break;
+    }
+  }
+  return cost;
+}
+
+void compile(const qnn_circuit* c, Program* out) {
+  // The scheduler is greedy; its one real choice (diagonal first or exchange first) is made by trying
+  // each policy and keeping the cheapest program.
+  Program best;
+  double best_cost = 0;
+  for (int policy = 0; policy < 3; ++policy) {
+    Program cand;
+    Builder b{};
+    b.c = c; b.P = &cand; b.policy = policy;
+    if (!b.run()) {
+      cand.ok = false;
+      cand.ops.clear();
+      if (!best.ok && best.why_not.empty()) best = cand;
+      continue;
+    }
+    const double cost = program_cost(cand);
+    if (!best.ok || cost < best_cost) { best = cand; best_cost = cost; }
+  }
+  *out = best;
+}
+
+std::string describe(const Program& p) {
+  std::ostringstream o;
+  o << "{\"ok\": " << (p.ok ? "true" : "false") << ", \"why_not\": \"" << p.why_not << "\"";
+  if (!p.ok) { o << "}"; return o.str(); }
+  o << ", \"n\": " << p.n << ", \"tb\": " << p.tb << ", \"n_acc\": " << p.n_acc;
+  auto arr = [&](const char* name, const int* v, int cnt) {
+    o << ", \"" << name << "\": [";
+    for (int i = 0; i < cnt; ++i) o << (i ? ", " : "") << v[i];
+    o << "]";
+  };
+  arr("initial_bit_of_wire", p.initial_bit_of_wire, p.n);
+  arr("final_bit_of_wire", p.final_bit_of_wire, p.n);
+  o << ", \"ops\": [";
+  for (size_t i = 0; i < p.ops.size(); ++i) {
+    const MicroOp& m = p.ops[i];
+    o << (i ? ", " : "") << "[" << m.kind << ", " << m.a << ", " << m.b << ", " << m.idx << ", " << m.acc << ", " << m.aux << "]";
+  }
+  o << "], \"coef_ops\": [";
+  for (size_t i = 0; i < p.coef_ops.size(); ++i) {
+    const DevOp& d = p.coef_ops[i];
+    o << (i ? ", " : "") << "{\"kind\": " << d.kind << ", \"src\": [" << d.src[0] << ", " << d.src[1] << ", " << d.src[2]
+      << "], \"value\": [" << d.value[0] << ", " << d.value[1] << ", " << d.value[2] << "]}";
+  }
+  o << "], \"diags\": [";
+  for (size_t i = 0; i < p.diags.size(); ++i) {
+    const DiagDesc& D = p.diags[i];
+    o << (i ? ", " : "") << "{\"is_reg\": " << D.is_reg << ", \"table\": " << D.table << ", \"terms\": [";
+    for (int t = 0; t < D.n_terms; ++t) {
+      const DiagTerm& T = p.terms[D.first_term + t];
+      o << (t ? ", " : "") << "[" << T.kind << ", " << T.src << ", " << T.value << ", " << T.bit0 << ", " << T.bit1 << "]";
+    }
+    o << "], \"acc_reg\": [";
+    for (int r = 0; r < kR; ++r) o << (r ? ", " : "") << D.acc_reg[r];
+    o << "], \"acc_lane\": [";
+    for (int r = 0; r < 5; ++r) o << (r ? ", " : "") << D.acc_lane[r];
+    o << "]}";
+  }
+  o << "], \"exchanges\": [";
+  for (size_t i = 0; i < p.exchanges.size(); ++i) {
+    const Exchange& X = p.exchanges[i];
+    o << (i ? ", " : "") << "{";
+    const uint32_t* tabs[4] = {X.wbase, X.woff, X.rbase, X.roff};
+    const char* names[4] = {"wbase", "woff", "rbase", "roff"};
+    for (int t = 0; t < 4; ++t) {
+      o << (t ? ", " : "") << "\"" << names[t] << "\": [";
+      for (int v = 0; v < 32; ++v) o << (v ? ", " : "") << tabs[t][v];
+      o << "]";
+    }
+    o << "}";
+  }
+  o << "], \"slots\": [";
+  for (size_t i = 0; i < p.slots.size(); ++i) {
+    const GradSlot& s = p.slots[i];
+    o << (i ? ", " : "") << "[" << s.weight << ", " << s.kind << ", " << s.acc << ", " << s.coef << ", " << s.angle << "]";
+  }
+  o << "]}";
+  return o.str();
+}
+
+}  // namespace vm

@@ -151,3 +151,50 @@ def test_error_paths():
     with pytest.raises(ValueError):
         qris_b200.qnn_apply(circ, torch.zeros(8, 5, device="cuda"), w)
     assert qris_b200.qnn_forward_raw(circ, torch.zeros(0, 4, device="cuda"), w).shape == (0, 4)
+
+
+def _plan(circ, B):
+    return qris_b200._lib.lib().qnn_circuit_plan(circ.handle(0), B).decode()
+
+
+def test_kernel_family_selection_and_both_families_agree(monkeypatch):
+    """n in [5, 10] runs on the register-resident VM; QNN_DISABLE_VM=1 (read at circuit creation) keeps
+    a circuit on the generic interpreter.  Both must match the oracle and each other."""
+    for make in (lambda: qris_b200.reference_circuit(6, 3), lambda: qris_b200.u3cu3_circuit(10, 2),
+                 lambda: qris_b200.u3cu3_circuit(7, 2), lambda: qris_b200.reference_circuit(9, 2)):
+        monkeypatch.delenv("QNN_DISABLE_VM", raising=False)
+        fast = make()
+        assert _plan(fast, 64) == "vm-register"
+        monkeypatch.setenv("QNN_DISABLE_VM", "1")
+        slow = make()
+        assert _plan(slow, 64).startswith("generic")
+        monkeypatch.delenv("QNN_DISABLE_VM", raising=False)
+        x, w, gy = seeded_inputs(fast, 77, seed=5)
+        a, b = run_gpu(fast, x, w, gy), run_gpu(slow, x, w, gy)
+        for u, v, name in zip(a, b, ("y", "gx", "gw")):
+            assert_close(u, v, rel=2e-5, scale=float(np.abs(v).max()), what=name)
+        check_against_oracle(slow, 33, seed=1)
+    assert _plan(qris_b200.reference_circuit(4, 1), 8).startswith("generic")
+    assert _plan(qris_b200.reference_circuit(12, 1), 8).startswith("generic")
+
+
+@pytest.mark.parametrize("n", [5, 6, 7, 8, 9, 10])
+@pytest.mark.parametrize("B", [1, 3, 32, 1000])
+def test_vm_all_widths_and_ragged_batches(n, B):
+    """Every lane/sample geometry of the VM (2^(n-5) lanes per sample), including partially filled warps."""
+    check_against_oracle(qris_b200.reference_circuit(n, 2), B, seed=n * 7 + B)
+    check_against_oracle(qris_b200.u3cu3_circuit(n, 1), B, seed=n * 11 + B)
+
+
+def test_vm_irregular_circuit():
+    Op = qris_b200.Op
+    n = 7
+    ops = [Op("RY", (i,), (("x", i),)) for i in range(n)]
+    ops += [Op("CNOT", (0, 6)), Op("RZ", (0,), (("w", 0),)), Op("RZ", (6,), (("w", 1),)), Op("RX", (6,), (("w", 2),)),
+            Op("CZ", (1, 5)), Op("CNOT", (5, 1)), Op("CNOT", (1, 5)), Op("U3", (5,), (("w", 3), ("c", 0.4), ("w", 4))),
+            Op("CU3", (6, 2), (("w", 5), ("w", 6), ("w", 7))), Op("CNOT", (2, 3)), Op("RY", (3,), (("x", 0),)),
+            Op("CZ", (3, 4)), Op("RZ", (4,), (("c", 1.3),)), Op("CNOT", (4, 0)), Op("CNOT", (0, 4)), Op("RY", (0,), (("w", 8),)),
+            Op("RX", (2,), (("w", 2),)), Op("CU3", (0, 1), (("c", 0.2), ("w", 6), ("c", -0.7)))]
+    circ = qris_b200.Circuit(n, ops, n_inputs=n, n_weights=9)
+    assert _plan(circ, 10) == "vm-register"
+    check_against_oracle(circ, 45, seed=2)

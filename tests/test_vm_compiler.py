@@ -1,0 +1,57 @@
+"""CPU: the VM's host compiler (csrc/qnn_vm_compile.cpp) checked by emulating its micro-op program in
+numpy and comparing with the oracle; also checks every exchange for bank-conflict freedom."""
+import numpy as np
+import pytest
+import torch
+
+import qris_b200
+from helpers import oracle_ops
+from oracle import qnn_oracle as O
+from vm_emulator import emulate_forward
+
+
+def _check(circ, seed=0):
+    desc = circ.describe()
+    assert desc["ok"], desc["why_not"]
+    spw = 32 >> desc["tb"]
+    rng = np.random.default_rng(seed)
+    x = rng.uniform(-1, 1, (spw, circ.n_inputs))
+    w = rng.uniform(0, 2 * np.pi, circ.n_weights)
+    y, stats = emulate_forward(desc, x, w)
+    yo = O.simulate(oracle_ops(circ), circ.n_qubits, torch.tensor(x), torch.tensor(w)).numpy()
+    np.testing.assert_allclose(y, yo, atol=1e-12)
+    return desc, stats
+
+
+@pytest.mark.parametrize("n", [5, 6, 7, 8, 9, 10])
+@pytest.mark.parametrize("L", [1, 3])
+def test_reference_circuit_program(n, L):
+    desc, stats = _check(qris_b200.reference_circuit(n, L), seed=n + L)
+    assert stats["xchg"] <= 2 * L + 1          # CNOT rings ride along with the exchanges
+    assert stats["diag"] + stats["diag_reg"] <= L
+
+
+@pytest.mark.parametrize("n,L", [(5, 2), (6, 2), (8, 1), (10, 3)])
+def test_u3cu3_program(n, L):
+    desc, stats = _check(qris_b200.u3cu3_circuit(n, L), seed=n)
+    assert stats["cg_l"] + stats["cg_p"] == n * L
+    if n == 10 and L == 3:
+        assert stats["xchg"] <= 2 * L and stats["cg_p"] <= 2 * L
+
+
+def test_irregular_program():
+    Op = qris_b200.Op
+    n = 7
+    ops = [Op("RY", (i,), (("x", i),)) for i in range(n)]
+    ops += [Op("CNOT", (0, 6)), Op("RZ", (0,), (("w", 0),)), Op("RZ", (6,), (("w", 1),)), Op("RX", (6,), (("w", 2),)),
+            Op("CZ", (1, 5)), Op("CNOT", (5, 1)), Op("CNOT", (1, 5)), Op("U3", (5,), (("w", 3), ("c", 0.4), ("w", 4))),
+            Op("CU3", (6, 2), (("w", 5), ("w", 6), ("w", 7))), Op("CNOT", (2, 3)), Op("RY", (3,), (("x", 0),)),
+            Op("CZ", (3, 4)), Op("RZ", (4,), (("c", 1.3),)), Op("CNOT", (4, 0)), Op("CNOT", (0, 4)), Op("RY", (0,), (("w", 8),))]
+    _check(qris_b200.Circuit(n, ops, n_inputs=n, n_weights=9), seed=3)
+
+
+def test_out_of_scope_circuits_report_why():
+    assert not qris_b200.reference_circuit(4, 1).describe()["ok"]
+    d = qris_b200.u3cu3_circuit(6, 1, encoder="amplitude").describe()
+    assert not d["ok"] and "amplitude" in d["why_not"]
+    assert not qris_b200.reference_circuit(12, 1).describe()["ok"]

@@ -1,0 +1,130 @@
+"""numpy emulator of the register-resident VM's micro-op program (csrc/qnn_vm.h), for CPU tests of the
+host compiler: layout tracking, merged diagonals, GF(2) exchanges.  Test infrastructure only.
+
+One warp is emulated: 32 lanes x 32 register amplitudes, 32 / 2^tb samples.  Exchanges go through an
+emulated 8 KB buffer with the program's XOR addressing, and every access is checked for shared-memory
+bank conflicts (64-bit accesses: the 16 lanes of a half-warp must hit 16 distinct 8-byte slots mod 16).
+"""
+import numpy as np
+
+SRC_CONST = -(2 ** 31)
+RX, RY, RZ, U3, CNOT, CZ, CU3 = range(7)
+(MOP_END, MOP_G1_REAL, MOP_G1_REAL_X, MOP_G1_GEN, MOP_CG1_L, MOP_CG1_P, MOP_DIAG, MOP_DIAG_REG, MOP_XCHG) = range(9)
+
+
+def _angle(src, value, w):
+    return value if src == SRC_CONST else w[src]
+
+
+def _matrix(kind, a):
+    if kind == RY:
+        c, s = np.cos(a[0] / 2), np.sin(a[0] / 2)
+        return np.array([[c, -s], [s, c]], complex)
+    if kind == RX:
+        c, s = np.cos(a[0] / 2), np.sin(a[0] / 2)
+        return np.array([[c, -1j * s], [-1j * s, c]], complex)
+    t, p, l = a
+    c, s = np.cos(t / 2), np.sin(t / 2)
+    return np.array([[c, -np.exp(1j * l) * s], [np.exp(1j * p) * s, np.exp(1j * (p + l)) * c]], complex)
+
+
+def _apply_reg(state, U, rbit, lane_mask=None, ctrl_rbit=None):
+    """state[lane, j]; apply U on register bit rbit for the selected lanes / control register bit."""
+    j = np.arange(32)
+    j0 = j[(j >> rbit) & 1 == 0]
+    if ctrl_rbit is not None:
+        j0 = j0[(j0 >> ctrl_rbit) & 1 == 1]
+    j1 = j0 | (1 << rbit)
+    lanes = np.arange(32) if lane_mask is None else np.nonzero(lane_mask)[0]
+    a0 = state[np.ix_(lanes, j0)].copy()
+    a1 = state[np.ix_(lanes, j1)].copy()
+    state[np.ix_(lanes, j0)] = U[0, 0] * a0 + U[0, 1] * a1
+    state[np.ix_(lanes, j1)] = U[1, 0] * a0 + U[1, 1] * a1
+
+
+def check_conflict_free(base, off):
+    for j in range(32):
+        for half in (0, 16):
+            slots = {((base[l] ^ off[j]) // 8) % 16 for l in range(half, half + 16)}
+            assert len(slots) == 16, "shared-memory bank conflict in an exchange"
+
+
+def emulate_forward(desc, x, w):
+    """x: (samples_per_warp, n_inputs); returns y (samples_per_warp, n)."""
+    assert desc["ok"]
+    n, tb = desc["n"], desc["tb"]
+    T = 1 << tb
+    spw = 32 // T
+    assert x.shape[0] == spw
+    state = np.zeros((32, 32), complex)
+    for s in range(spw):
+        state[s * T, 0] = 1.0
+    lane = np.arange(32)
+    lis = lane % T                       # lane in sample
+    samp = lane // T
+    stats = {"xchg": 0, "diag": 0, "diag_reg": 0, "g1": 0, "cg_l": 0, "cg_p": 0}
+    for kind, a, b, idx, acc, aux in desc["ops"]:
+        if kind == MOP_END:
+            break
+        if kind == MOP_G1_REAL or kind == MOP_G1_GEN:
+            co = desc["coef_ops"][idx]
+            U = _matrix(co["kind"], [_angle(s_, v_, w) for s_, v_ in zip(co["src"], co["value"])])
+            _apply_reg(state, U, a)
+            stats["g1"] += 1
+        elif kind == MOP_G1_REAL_X:
+            for s in range(spw):
+                _apply_reg(state, _matrix(RY, [x[s, idx]]), a, lane_mask=(samp == s))
+            stats["g1"] += 1
+        elif kind in (MOP_CG1_L, MOP_CG1_P):
+            co = desc["coef_ops"][idx]
+            U = _matrix(U3, [_angle(s_, v_, w) for s_, v_ in zip(co["src"], co["value"])])
+            if kind == MOP_CG1_L:
+                _apply_reg(state, U, a, ctrl_rbit=b)
+                stats["cg_l"] += 1
+            else:
+                par = np.array([bin(int(v) & aux).count("1") & 1 for v in lis], bool)
+                _apply_reg(state, U, a, lane_mask=par)
+                stats["cg_p"] += 1
+        elif kind in (MOP_DIAG, MOP_DIAG_REG):
+            D = desc["diags"][aux]
+            assert bool(D["is_reg"]) == (kind == MOP_DIAG_REG)
+            j = np.arange(32)
+            p = j[None, :] | (lis[:, None] << 5)         # physical index of (lane, j) within its sample
+            ang = np.zeros((32, 32))
+            for tkind, src, value, bit0, bit1 in D["terms"]:
+                if tkind == 0:
+                    z = 1 - 2 * ((p >> bit0) & 1)
+                    ang += -0.5 * _angle(src, value, w) * z
+                else:
+                    ang += np.pi * (((p >> bit0) & 1) & ((p >> bit1) & 1))
+                if kind == MOP_DIAG_REG:
+                    assert bit0 < 5 and bit1 < 5
+            state *= np.exp(1j * ang)
+            stats["diag" if kind == MOP_DIAG else "diag_reg"] += 1
+        elif kind == MOP_XCHG:
+            X = desc["exchanges"][idx]
+            check_conflict_free(X["wbase"], X["woff"])
+            check_conflict_free(X["rbase"], X["roff"])
+            buf = {}
+            for l in range(32):
+                for jj in range(32):
+                    addr = X["wbase"][l] ^ X["woff"][jj]
+                    assert addr % 8 == 0 and 0 <= addr < 8192 and addr not in buf
+                    buf[addr] = state[l, jj]
+            new = np.empty_like(state)
+            for l in range(32):
+                for jj in range(32):
+                    new[l, jj] = buf[X["rbase"][l] ^ X["roff"][jj]]
+            state = new
+            stats["xchg"] += 1
+        else:
+            raise ValueError(f"unknown micro-op {kind}")
+    prob = np.abs(state) ** 2
+    j = np.arange(32)
+    p = j[None, :] | (lis[:, None] << 5)
+    y = np.zeros((spw, n))
+    for wire, bit in enumerate(desc["final_bit_of_wire"]):
+        z = 1 - 2 * ((p >> bit) & 1)
+        for s in range(spw):
+            y[s, wire] = (prob * z)[samp == s].sum()
+    return y, stats
