@@ -12,13 +12,13 @@
 // gradients are taken from (lam, psi) pairs:
 //   real rotation    dL/dtheta = Re sum_pairs conj(lam1) psi0 - conj(lam0) psi1
 //   diagonal term    dL/dphi   = sum_p z_bit(p) Im(conj(lam_p) psi_p)
-//   general 2x2      T_ab = sum conj(lam_a) psi_b, finished as 2 Re sum G_ab T_ab in k_vm_finalize.
+//   phase on |1>     dL/dphi   = -2 sum_pairs Im(conj(lam1) psi1)        (the two phases of a CU3)
 // Weight-gradient accumulators are reduced over the warp by shuffles, kept per warp in shared memory,
 // summed per CTA in a fixed order and finished by k_vm_finalize: deterministic.
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 
-#include "qnn_gates.cuh"
 #include "qnn_vm.h"
 
 namespace vm {
@@ -61,88 +61,118 @@ __device__ __forceinline__ constexpr int cpair_lo(int i) {
 }
 
 // ---- gate bodies ---------------------------------------------------------------------------------
+// The state is kept as (re, im) register pairs and all arithmetic uses Blackwell's packed FP32x2
+// instructions (FFMA2 / FMUL2 / FADD2, sm_100+): one issue slot per two FMAs.  Scalar three-register
+// FFMAs issue at only ~2/3 rate on this part (register-bank read ports; profiles/experiments/fma_rate.cu),
+// so the packed form is what lets the FMA pipe, not the issue port, be the limit.
+__device__ __forceinline__ float2 mul2(float s, float2 a) { return __fmul2_rn(make_float2(s, s), a); }
+__device__ __forceinline__ float2 fma2(float s, float2 a, float2 c) { return __ffma2_rn(make_float2(s, s), a, c); }
+__device__ __forceinline__ float2 swp(float2 a) { return make_float2(a.y, a.x); }
+
+// Real rotation [[c,-s],[s,c]] (c,s = cos,sin(phi)) as three in-place shears
+//   a0 += al*a1;  a1 += be*a0;  a0 += al*a1       al = -tan(phi/2), be = sin(phi)
+// 3 packed FMAs per amplitude pair, no temporaries; the inverse uses (-al, -be).  phi is range-reduced to
+// [-pi/2, pi/2] when the coefficients are made, so |al| <= 0.415.
 template <int RB>
-__device__ __forceinline__ void g1_real(float (&re)[NA], float (&im)[NA], float c, float s) {
+__device__ __forceinline__ void rot(float2 (&st)[NA], float al, float be) {
 #pragma unroll
   for (int i = 0; i < NA / 2; ++i) {
     const int j0 = pair_lo<RB>(i), j1 = j0 | (1 << RB);
-    const float a0 = re[j0], a1 = re[j1], b0 = im[j0], b1 = im[j1];
-    re[j0] = fmaf(-s, a1, c * a0); re[j1] = fmaf(s, a0, c * a1);
-    im[j0] = fmaf(-s, b1, c * b0); im[j1] = fmaf(s, b0, c * b1);
+    st[j0] = fma2(al, st[j1], st[j0]);
+    st[j1] = fma2(be, st[j0], st[j1]);
+    st[j0] = fma2(al, st[j1], st[j0]);
   }
 }
+// Re sum conj(l1) p0 - conj(l0) p1  (gradient of a rotation angle, from the AFTER vectors)
+__device__ __forceinline__ void rot_grad_acc(float2& v0, float2& v1, float2 p0, float2 p1, float2 l0, float2 l1) {
+  v0 = __ffma2_rn(l1, p0, v0);
+  v1 = __ffma2_rn(l0, p1, v1);
+}
+template <int RB>
+__device__ __forceinline__ float rot_grad(const float2 (&ps)[NA], const float2 (&ls)[NA]) {
+  float2 v0 = make_float2(0.f, 0.f), v1 = make_float2(0.f, 0.f);
+#pragma unroll
+  for (int i = 0; i < NA / 2; ++i) {
+    const int j0 = pair_lo<RB>(i), j1 = j0 | (1 << RB);
+    rot_grad_acc(v0, v1, ps[j0], ps[j1], ls[j0], ls[j1]);
+  }
+  return (v0.x + v0.y) - (v1.x + v1.y);
+}
 
-struct U2 { float r00, i00, r01, i01, r10, i10, r11, i11; };
+// a <- e * a for a unit complex e = (er, ei), in place: er*a + (-ei, ei) (.) swap(a)
+__device__ __forceinline__ float2 cmul(float er, float2 ei2, float2 a) { return __ffma2_rn(ei2, swp(a), mul2(er, a)); }
 
-__device__ __forceinline__ U2 load_u(const float* c) {
+// Controlled U3 on one control=1 pair: diag(1, e^{i phi}) * m0 R(phi') * diag(1, e^{i lambda}); the sign
+// m0 = +-1 of the range reduction is folded into the first phase (a1) and one multiply (a0).
+struct Cu3 {
+  float al, be, m0, elr, epr;
+  float2 eli, epi;     // (-im, +im) of m0*e^{i lambda} and e^{i phi}
+};
+__device__ __forceinline__ Cu3 load_cu3(const float* c, bool inverse) {
   const float4 a = *reinterpret_cast<const float4*>(c), b = *reinterpret_cast<const float4*>(c + 4);
-  return U2{a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-}
-__device__ __forceinline__ U2 dagger(const U2& u) { return U2{u.r00, -u.i00, u.r10, -u.i10, u.r01, -u.i01, u.r11, -u.i11}; }
-
-__device__ __forceinline__ void apply_pair(const U2& u, float& r0, float& i0, float& r1, float& i1) {
-  const float a0 = r0, b0 = i0, a1 = r1, b1 = i1;
-  r0 = fmaf(-u.i01, b1, fmaf(u.r01, a1, fmaf(-u.i00, b0, u.r00 * a0)));
-  i0 = fmaf(u.i01, a1, fmaf(u.r01, b1, fmaf(u.i00, a0, u.r00 * b0)));
-  r1 = fmaf(-u.i11, b1, fmaf(u.r11, a1, fmaf(-u.i10, b0, u.r10 * a0)));
-  i1 = fmaf(u.i11, a1, fmaf(u.r11, b1, fmaf(u.i10, a0, u.r10 * b0)));
-}
-
-template <int RB>
-__device__ __forceinline__ void g1_gen(float (&re)[NA], float (&im)[NA], const U2& u) {
-#pragma unroll
-  for (int i = 0; i < NA / 2; ++i) {
-    const int j0 = pair_lo<RB>(i), j1 = j0 | (1 << RB);
-    apply_pair(u, re[j0], im[j0], re[j1], im[j1]);
+  Cu3 g;
+  g.m0 = a.z;
+  if (!inverse) {
+    g.al = a.x; g.be = a.y; g.elr = a.z * b.x; g.eli = make_float2(-a.z * b.y, a.z * b.y);
+    g.epr = b.z; g.epi = make_float2(-b.w, b.w);
+  } else {   // conjugate phases, opposite shears
+    g.al = -a.x; g.be = -a.y; g.elr = a.z * b.x; g.eli = make_float2(a.z * b.y, -a.z * b.y);
+    g.epr = b.z; g.epi = make_float2(b.w, -b.w);
   }
+  return g;
+}
+__device__ __forceinline__ void cu3_pair(const Cu3& g, float2& a0, float2& a1) {
+  a1 = cmul(g.elr, g.eli, a1);
+  a0 = mul2(g.m0, a0);
+  a0 = fma2(g.al, a1, a0);
+  a1 = fma2(g.be, a0, a1);
+  a0 = fma2(g.al, a1, a0);
+  a1 = cmul(g.epr, g.epi, a1);
+}
+// Reverse step on one pair, for psi (p) and lam (l) together, g = load_cu3(.., inverse=true).
+// Accumulates (as packed pairs, finished by the caller): q_phi, v_theta0/1, q_lambda.
+struct Cu3Acc { float2 qp, v0, v1, ql; };
+__device__ __forceinline__ void cu3_pair_bwd(const Cu3& g, float2& p0, float2& p1, float2& l0, float2& l1, Cu3Acc& A) {
+  A.qp = __ffma2_rn(l1, swp(p1), A.qp);           // (l.re p.im, l.im p.re): Im(conj(l1) p1) = x - y
+  p1 = cmul(g.epr, g.epi, p1); l1 = cmul(g.epr, g.epi, l1);
+  rot_grad_acc(A.v0, A.v1, p0, p1, l0, l1);
+  p0 = fma2(g.al, p1, p0); p1 = fma2(g.be, p0, p1); p0 = fma2(g.al, p1, p0);
+  l0 = fma2(g.al, l1, l0); l1 = fma2(g.be, l0, l1); l0 = fma2(g.al, l1, l0);
+  p0 = mul2(g.m0, p0); l0 = mul2(g.m0, l0);
+  A.ql = __ffma2_rn(l1, swp(p1), A.ql);
+  p1 = cmul(g.elr, g.eli, p1); l1 = cmul(g.elr, g.eli, l1);
 }
 template <int RT, int RC>
-__device__ __forceinline__ void cg1_loc(float (&re)[NA], float (&im)[NA], const U2& u) {
+__device__ __forceinline__ void cu3_loc(float2 (&st)[NA], const Cu3& g) {
 #pragma unroll
   for (int i = 0; i < NA / 4; ++i) {
     const int j0 = cpair_lo<RT, RC>(i), j1 = j0 | (1 << RT);
-    apply_pair(u, re[j0], im[j0], re[j1], im[j1]);
+    cu3_pair(g, st[j0], st[j1]);
   }
 }
-
-// T += conj(l_a) p_b over the pairs of register bit RB (T as T00,T01,T10,T11, (re, im))
-__device__ __forceinline__ void t_acc(float (&T)[8], float p0r, float p0i, float p1r, float p1i, float l0r, float l0i,
-                                      float l1r, float l1i) {
-  T[0] = fmaf(l0i, p0i, fmaf(l0r, p0r, T[0])); T[1] = fmaf(-l0i, p0r, fmaf(l0r, p0i, T[1]));
-  T[2] = fmaf(l0i, p1i, fmaf(l0r, p1r, T[2])); T[3] = fmaf(-l0i, p1r, fmaf(l0r, p1i, T[3]));
-  T[4] = fmaf(l1i, p0i, fmaf(l1r, p0r, T[4])); T[5] = fmaf(-l1i, p0r, fmaf(l1r, p0i, T[5]));
-  T[6] = fmaf(l1i, p1i, fmaf(l1r, p1r, T[6])); T[7] = fmaf(-l1i, p1r, fmaf(l1r, p1i, T[7]));
-}
 template <int RB>
-__device__ __forceinline__ void g1_gen_T(const float (&pr)[NA], const float (&pi)[NA], const float (&lr)[NA],
-                                         const float (&li)[NA], float (&T)[8]) {
+__device__ __forceinline__ void cu3_all(float2 (&st)[NA], const Cu3& g) {
 #pragma unroll
   for (int i = 0; i < NA / 2; ++i) {
     const int j0 = pair_lo<RB>(i), j1 = j0 | (1 << RB);
-    t_acc(T, pr[j0], pi[j0], pr[j1], pi[j1], lr[j0], li[j0], lr[j1], li[j1]);
+    cu3_pair(g, st[j0], st[j1]);
   }
 }
 template <int RT, int RC>
-__device__ __forceinline__ void cg1_loc_T(const float (&pr)[NA], const float (&pi)[NA], const float (&lr)[NA],
-                                          const float (&li)[NA], float (&T)[8]) {
+__device__ __forceinline__ void cu3_loc_bwd(float2 (&ps)[NA], float2 (&ls)[NA], const Cu3& g, Cu3Acc& A) {
 #pragma unroll
   for (int i = 0; i < NA / 4; ++i) {
     const int j0 = cpair_lo<RT, RC>(i), j1 = j0 | (1 << RT);
-    t_acc(T, pr[j0], pi[j0], pr[j1], pi[j1], lr[j0], li[j0], lr[j1], li[j1]);
+    cu3_pair_bwd(g, ps[j0], ps[j1], ls[j0], ls[j1], A);
   }
 }
-// Re sum conj(l1) p0 - conj(l0) p1  (gradient of a real rotation angle, from the AFTER vectors)
 template <int RB>
-__device__ __forceinline__ float g1_real_grad(const float (&pr)[NA], const float (&pi)[NA], const float (&lr)[NA],
-                                              const float (&li)[NA]) {
-  float v0 = 0.f, v1 = 0.f;
+__device__ __forceinline__ void cu3_all_bwd(float2 (&ps)[NA], float2 (&ls)[NA], const Cu3& g, Cu3Acc& A) {
 #pragma unroll
   for (int i = 0; i < NA / 2; ++i) {
     const int j0 = pair_lo<RB>(i), j1 = j0 | (1 << RB);
-    v0 = fmaf(lr[j1], pr[j0], v0); v0 = fmaf(li[j1], pi[j0], v0);
-    v1 = fmaf(lr[j0], pr[j1], v1); v1 = fmaf(li[j0], pi[j1], v1);
+    cu3_pair_bwd(g, ps[j0], ps[j1], ls[j0], ls[j1], A);
   }
-  return v0 - v1;
 }
 
 #define RB_SWITCH(rb, CALL)          \
@@ -172,23 +202,24 @@ __device__ __forceinline__ float g1_real_grad(const float (&pr)[NA], const float
   }
 
 // ---- sums over the 32 register amplitudes: total and, per register bit r, the signed sum -------------
-// S[r] = sum_j (-1)^{j_r} v_j, computed with a shared tree (61 adds).
+// S[r] = sum_j (-1)^{j_r} v_j with a shared tree (61 packed adds); v_j are pairs, reduced per half.
 template <typename F>
-__device__ __forceinline__ void signed_sums(F f, float& total, float (&S)[kR]) {
-  float a[16], o0 = 0.f;
+__device__ __forceinline__ void signed_sums2(F f, float2& total, float2 (&S)[kR]) {
+  const float2 z = make_float2(0.f, 0.f);
+  float2 a[16], o0 = z;
 #pragma unroll
-  for (int i = 0; i < 16; ++i) { const float e = f(2 * i), o = f(2 * i + 1); a[i] = e + o; o0 += o; }
-  float b[8], o1 = 0.f;
+  for (int i = 0; i < 16; ++i) { const float2 e = f(2 * i), o = f(2 * i + 1); a[i] = __fadd2_rn(e, o); o0 = __fadd2_rn(o0, o); }
+  float2 b[8], o1 = z;
 #pragma unroll
-  for (int i = 0; i < 8; ++i) { b[i] = a[2 * i] + a[2 * i + 1]; o1 += a[2 * i + 1]; }
-  float c[4], o2 = 0.f;
+  for (int i = 0; i < 8; ++i) { b[i] = __fadd2_rn(a[2 * i], a[2 * i + 1]); o1 = __fadd2_rn(o1, a[2 * i + 1]); }
+  float2 c[4], o2 = z;
 #pragma unroll
-  for (int i = 0; i < 4; ++i) { c[i] = b[2 * i] + b[2 * i + 1]; o2 += b[2 * i + 1]; }
-  const float d0 = c[0] + c[1], d1 = c[2] + c[3];
-  const float o3 = c[1] + c[3], o4 = d1;
-  total = d0 + d1;
-  S[0] = fmaf(-2.f, o0, total); S[1] = fmaf(-2.f, o1, total); S[2] = fmaf(-2.f, o2, total);
-  S[3] = fmaf(-2.f, o3, total); S[4] = fmaf(-2.f, o4, total);
+  for (int i = 0; i < 4; ++i) { c[i] = __fadd2_rn(b[2 * i], b[2 * i + 1]); o2 = __fadd2_rn(o2, b[2 * i + 1]); }
+  const float2 d0 = __fadd2_rn(c[0], c[1]), d1 = __fadd2_rn(c[2], c[3]);
+  const float2 o3 = __fadd2_rn(c[1], c[3]), o4 = d1;
+  total = __fadd2_rn(d0, d1);
+  S[0] = fma2(-2.f, o0, total); S[1] = fma2(-2.f, o1, total); S[2] = fma2(-2.f, o2, total);
+  S[3] = fma2(-2.f, o3, total); S[4] = fma2(-2.f, o4, total);
 }
 
 __device__ __forceinline__ float warp_sum(float v) {   // over all 32 lanes
@@ -200,41 +231,28 @@ __device__ __forceinline__ float sample_sum(float v, int tb) {   // over the 2^t
   for (int b = 0; b < tb; ++b) v += __shfl_xor_sync(0xffffffffu, v, 1 << b);
   return v;
 }
-// 8 values summed over the warp with the halving butterfly: afterwards lane l holds component
-// (l >> 2) & 7 ... precisely: comp = 4*bit4 + 2*bit3 + bit2 of the lane, fully reduced.
-__device__ __forceinline__ float warp_sum8(const float (&T)[8], int lane) {
-  float k4[4];
+// 4 values summed over the warp with the halving butterfly: afterwards lane l holds component
+// 2*bit4 + bit3 of l, fully reduced (9 shuffles instead of 20).
+__device__ __forceinline__ float warp_sum4(float t0, float t1, float t2, float t3, int lane) {
+  float k0, k1;
   {
     const bool up = lane & 16;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const float keep = up ? T[4 + i] : T[i], send = up ? T[i] : T[4 + i];
-      k4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-    }
+    k0 = (up ? t2 : t0) + __shfl_xor_sync(0xffffffffu, up ? t0 : t2, 16);
+    k1 = (up ? t3 : t1) + __shfl_xor_sync(0xffffffffu, up ? t1 : t3, 16);
   }
-  float k2[2];
+  float k;
   {
     const bool up = lane & 8;
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-      const float keep = up ? k4[2 + i] : k4[i], send = up ? k4[i] : k4[2 + i];
-      k2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-    }
+    k = (up ? k1 : k0) + __shfl_xor_sync(0xffffffffu, up ? k0 : k1, 8);
   }
-  float k1;
-  {
-    const bool up = lane & 4;
-    const float keep = up ? k2[1] : k2[0], send = up ? k2[0] : k2[1];
-    k1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-  }
-  k1 += __shfl_xor_sync(0xffffffffu, k1, 2);
-  k1 += __shfl_xor_sync(0xffffffffu, k1, 1);
-  return k1;
+  k += __shfl_xor_sync(0xffffffffu, k, 4);
+  k += __shfl_xor_sync(0xffffffffu, k, 2);
+  k += __shfl_xor_sync(0xffffffffu, k, 1);
+  return k;
 }
 
 // ---- exchange ---------------------------------------------------------------------------------------
-__device__ __forceinline__ void exchange(float (&re)[NA], float (&im)[NA], uint32_t buf, const Exchange* X, int lane,
-                                         bool reverse) {
+__device__ __forceinline__ void exchange(float2 (&st)[NA], uint32_t buf, const Exchange* X, int lane, bool reverse) {
   const uint32_t* wbase = reverse ? X->rbase : X->wbase;
   const uint32_t* woff = reverse ? X->roff : X->woff;
   const uint32_t* rbase = reverse ? X->wbase : X->rbase;
@@ -244,33 +262,43 @@ __device__ __forceinline__ void exchange(float (&re)[NA], float (&im)[NA], uint3
 #pragma unroll
   for (int q = 0; q < NA / 4; ++q) {
     const uint4 o = *reinterpret_cast<const uint4*>(woff + 4 * q);
-    sts64(wa ^ o.x, re[4 * q + 0], im[4 * q + 0]);
-    sts64(wa ^ o.y, re[4 * q + 1], im[4 * q + 1]);
-    sts64(wa ^ o.z, re[4 * q + 2], im[4 * q + 2]);
-    sts64(wa ^ o.w, re[4 * q + 3], im[4 * q + 3]);
+    sts64(wa ^ o.x, st[4 * q + 0].x, st[4 * q + 0].y);
+    sts64(wa ^ o.y, st[4 * q + 1].x, st[4 * q + 1].y);
+    sts64(wa ^ o.z, st[4 * q + 2].x, st[4 * q + 2].y);
+    sts64(wa ^ o.w, st[4 * q + 3].x, st[4 * q + 3].y);
   }
   __syncwarp();
 #pragma unroll
   for (int q = 0; q < NA / 4; ++q) {
     const uint4 o = *reinterpret_cast<const uint4*>(roff + 4 * q);
-    lds64(ra ^ o.x, re[4 * q + 0], im[4 * q + 0]);
-    lds64(ra ^ o.y, re[4 * q + 1], im[4 * q + 1]);
-    lds64(ra ^ o.z, re[4 * q + 2], im[4 * q + 2]);
-    lds64(ra ^ o.w, re[4 * q + 3], im[4 * q + 3]);
+    lds64(ra ^ o.x, st[4 * q + 0].x, st[4 * q + 0].y);
+    lds64(ra ^ o.y, st[4 * q + 1].x, st[4 * q + 1].y);
+    lds64(ra ^ o.z, st[4 * q + 2].x, st[4 * q + 2].y);
+    lds64(ra ^ o.w, st[4 * q + 3].x, st[4 * q + 3].y);
   }
 }
 
-// multiply by a diagonal (optionally its conjugate): big table [j][lane] or register-only table [j]
-template <bool CONJ>
-__device__ __forceinline__ void diag_mul(float (&re)[NA], float (&im)[NA], const float2* tbl, int stride, int lane_off) {
+// multiply by a diagonal (optionally its conjugate): big table [j][lane] or register-only table [j].
+// d*a = d.re * a + (-d.im, d.im) (.) swap(a); one table load serves psi and lam in the backward pass.
+template <bool CONJ, bool TWO>
+__device__ __forceinline__ void diag_mul(float2 (&st)[NA], float2 (&st2)[NA], const float2* tbl, int stride, int lane_off) {
 #pragma unroll
   for (int j = 0; j < NA; ++j) {
     const float2 d = tbl[j * stride + lane_off];
-    const float dr = d.x, di = CONJ ? -d.y : d.y;
-    const float a = re[j], b = im[j];
-    re[j] = fmaf(-di, b, dr * a);
-    im[j] = fmaf(di, a, dr * b);
+    const float2 di = CONJ ? make_float2(d.y, -d.y) : make_float2(-d.y, d.y);
+    st[j] = __ffma2_rn(di, swp(st[j]), mul2(d.x, st[j]));
+    if (TWO) st2[j] = __ffma2_rn(di, swp(st2[j]), mul2(d.x, st2[j]));
   }
+}
+
+// Shear coefficients of RY(x) = R(x/2) for a per-sample angle: (al, be) = (-tan(phi'/2), sin phi') with
+// phi' = x/2 reduced to [-pi/2, pi/2]; the dropped sign (-1)^k is a global phase of the sample's state.
+__device__ __forceinline__ float2 rot_coef_x(float xv) {
+  float phi = 0.5f * xv;
+  phi = fmaf(-3.14159265358979323846f, rintf(phi * 0.318309886183790672f), phi);
+  float sh, ch;
+  sincosf(0.5f * phi, &sh, &ch);
+  return make_float2(-sh / ch, 2.f * sh * ch);
 }
 
 struct Smem {
@@ -349,7 +377,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
   float* const wacc = BWD ? S.wacc + (size_t)warp * max(a.n_acc, 1) : nullptr;
   float* const gxacc = BWD ? S.gxacc + (size_t)warp * spw * max(a.n_inputs, 1) : nullptr;
 
-  float pr[NA], pi[NA];
+  float2 ps[NA];
   const long long n_batches = (a.B + spw - 1) / spw;
   for (long long wb = (long long)blockIdx.x * WARPS + warp; wb < n_batches; wb += (long long)gridDim.x * WARPS) {
     const long long bs = wb * spw + siw;
@@ -357,62 +385,79 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
     const float* xrow = a.x + (size_t)(active ? bs : a.B - 1) * a.n_inputs;
 
 #pragma unroll
-    for (int j = 0; j < NA; ++j) { pr[j] = 0.f; pi[j] = 0.f; }
-    pr[0] = lis == 0 ? 1.f : 0.f;
+    for (int j = 0; j < NA; ++j) ps[j] = make_float2(0.f, 0.f);
+    ps[0].x = lis == 0 ? 1.f : 0.f;
 
     // ================= forward program =================
-    for (int pc = 0;; ++pc) {
-      const MicroOp op = S.ops[pc];
-      if (op.kind == MOP_END) break;
-      switch (op.kind) {
-        case MOP_G1_REAL: {
-          const float c = S.coef[op.idx * 8 + 0], s = S.coef[op.idx * 8 + 4];
-#define CALL(RB) g1_real<RB>(pr, pi, c, s)
-          RB_SWITCH(op.a, CALL)
-#undef CALL
-        } break;
-        case MOP_G1_REAL_X: {
-          float s, c;
-          sincosf(0.5f * xrow[op.idx], &s, &c);
-#define CALL(RB) g1_real<RB>(pr, pi, c, s)
-          RB_SWITCH(op.a, CALL)
-#undef CALL
-        } break;
-        case MOP_G1_GEN: {
-          const U2 u = load_u(S.coef + op.idx * 8);
-#define CALL(RB) g1_gen<RB>(pr, pi, u)
-          RB_SWITCH(op.a, CALL)
-#undef CALL
-        } break;
-        case MOP_CG1_L: {
-          const U2 u = load_u(S.coef + op.idx * 8);
-          const int rc = op.b;
-#define CALL(RT, RC) cg1_loc<RT, RC>(pr, pi, u)
-          RTC_SWITCH(op.a, CALL)
-#undef CALL
-        } break;
-        case MOP_CG1_P: {
-          if (__popc(lis & op.aux) & 1) {
-            const U2 u = load_u(S.coef + op.idx * 8);
-#define CALL(RB) g1_gen<RB>(pr, pi, u)
+    {
+      MicroOp op = S.ops[0];
+      for (int pc = 0; op.kind != MOP_END; ++pc) {
+        const MicroOp next = S.ops[pc + 1];    // fetched early: hides the shared-memory latency of the dispatch
+        switch (op.kind) {
+          case MOP_ROT: {
+            const float2 ab = *reinterpret_cast<const float2*>(S.coef + op.idx * 8);
+#define CALL(RB) rot<RB>(ps, ab.x, ab.y)
             RB_SWITCH(op.a, CALL)
 #undef CALL
-          }
-        } break;
-        case MOP_DIAG: diag_mul<false>(pr, pi, S.big + op.idx * 1024, 32, lane); break;
-        case MOP_DIAG_REG: diag_mul<false>(pr, pi, S.small + op.idx * 32, 1, 0); break;
-        case MOP_XCHG: exchange(pr, pi, S.xbuf, S.exchanges + op.idx, lane, false); break;
-        default: break;
+          } break;
+          case MOP_ROT_X: {
+            const float2 ab = rot_coef_x(xrow[op.idx]);
+#define CALL(RB) rot<RB>(ps, ab.x, ab.y)
+            RB_SWITCH(op.a, CALL)
+#undef CALL
+          } break;
+          case MOP_CU3_L: {
+            const Cu3 g = load_cu3(S.coef + op.idx * 8, false);
+            const int rc = op.b;
+#define CALL(RT, RC) cu3_loc<RT, RC>(ps, g)
+            RTC_SWITCH(op.a, CALL)
+#undef CALL
+          } break;
+          case MOP_CU3_P: {
+            if (__popc(lis & op.aux) & 1) {
+              const Cu3 g = load_cu3(S.coef + op.idx * 8, false);
+#define CALL(RB) cu3_all<RB>(ps, g)
+              RB_SWITCH(op.a, CALL)
+#undef CALL
+            }
+          } break;
+          case MOP_ROT5: {
+            float2 ab[5];
+#pragma unroll
+            for (int k = 0; k < 5; ++k) ab[k] = *reinterpret_cast<const float2*>(S.coef + (op.idx + ((op.aux >> (3 * k)) & 7)) * 8);
+            rot<0>(ps, ab[0].x, ab[0].y); rot<1>(ps, ab[1].x, ab[1].y); rot<2>(ps, ab[2].x, ab[2].y);
+            rot<3>(ps, ab[3].x, ab[3].y); rot<4>(ps, ab[4].x, ab[4].y);
+          } break;
+          case MOP_ROTX5: {
+            float2 ab[5];
+#pragma unroll
+            for (int k = 0; k < 5; ++k) ab[k] = rot_coef_x(xrow[(op.idx >> (5 * k)) & 31]);
+            rot<0>(ps, ab[0].x, ab[0].y); rot<1>(ps, ab[1].x, ab[1].y); rot<2>(ps, ab[2].x, ab[2].y);
+            rot<3>(ps, ab[3].x, ab[3].y); rot<4>(ps, ab[4].x, ab[4].y);
+          } break;
+          case MOP_CU3_CHAIN: {
+            { const Cu3 g = load_cu3(S.coef + (op.idx + 0) * 8, false); cu3_loc<1, 0>(ps, g); }
+            { const Cu3 g = load_cu3(S.coef + (op.idx + 1) * 8, false); cu3_loc<2, 1>(ps, g); }
+            { const Cu3 g = load_cu3(S.coef + (op.idx + 2) * 8, false); cu3_loc<3, 2>(ps, g); }
+            { const Cu3 g = load_cu3(S.coef + (op.idx + 3) * 8, false); cu3_loc<4, 3>(ps, g); }
+          } break;
+          case MOP_DIAG: diag_mul<false, false>(ps, ps, S.big + op.idx * 1024, 32, lane); break;
+          case MOP_DIAG_REG: diag_mul<false, false>(ps, ps, S.small + op.idx * 32, 1, 0); break;
+          case MOP_XCHG: exchange(ps, S.xbuf, S.exchanges + op.idx, lane, false); break;
+          default: break;
+        }
+        op = next;
       }
     }
 
     if constexpr (!BWD) {
       // ================= measurement: <Z> per physical bit =================
-      float tot, Sr[kR];
-      signed_sums([&](int j) { return fmaf(pr[j], pr[j], pi[j] * pi[j]); }, tot, Sr);
+      float2 tot2, S2[kR];
+      signed_sums2([&](int j) { return __fmul2_rn(ps[j], ps[j]); }, tot2, S2);
+      const float tot = tot2.x + tot2.y;
       float val[10];
 #pragma unroll
-      for (int r = 0; r < kR; ++r) val[r] = sample_sum(Sr[r], tb);
+      for (int r = 0; r < kR; ++r) val[r] = sample_sum(S2[r].x + S2[r].y, tb);
 #pragma unroll
       for (int b = 0; b < 5; ++b) val[kR + b] = (b < tb) ? sample_sum(((lis >> b) & 1) ? -tot : tot, tb) : 0.f;
       if (active && lis == 0) {
@@ -423,7 +468,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
       }
     } else {
       // ================= seed lam = (sum_q gy_q Z_q) psi =================
-      float lr[NA], li[NA];
+      float2 ls[NA];
       {
         float g[10];
         const float* gyrow = a.gy + (size_t)(active ? bs : 0) * a.n;
@@ -441,87 +486,122 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
           cj[j] = fmaf(-2.f, g[r], cj[j ^ low]);
         }
 #pragma unroll
-        for (int j = 0; j < NA; ++j) { lr[j] = cj[j] * pr[j]; li[j] = cj[j] * pi[j]; }
+        for (int j = 0; j < NA; ++j) ls[j] = mul2(cj[j], ps[j]);
       }
       // ================= reverse program =================
+      MicroOp op = S.ops[a.n_ops - 2];
       for (int pc = a.n_ops - 2; pc >= 0; --pc) {
-        const MicroOp op = S.ops[pc];
+        const MicroOp next = S.ops[pc > 0 ? pc - 1 : 0];
         switch (op.kind) {
-          case MOP_G1_REAL:
-          case MOP_G1_REAL_X: {
-            float s, c;
-            if (op.kind == MOP_G1_REAL) { c = S.coef[op.idx * 8 + 0]; s = S.coef[op.idx * 8 + 4]; }
-            else sincosf(0.5f * xrow[op.idx], &s, &c);
+          case MOP_ROT:
+          case MOP_ROT_X: {
+            const float2 ab = op.kind == MOP_ROT ? *reinterpret_cast<const float2*>(S.coef + op.idx * 8) : rot_coef_x(xrow[op.idx]);
             float v = 0.f;
-#define CALL(RB) { v = g1_real_grad<RB>(pr, pi, lr, li); g1_real<RB>(pr, pi, c, -s); g1_real<RB>(lr, li, c, -s); }
+#define CALL(RB) { v = rot_grad<RB>(ps, ls); rot<RB>(ps, -ab.x, -ab.y); rot<RB>(ls, -ab.x, -ab.y); }
             RB_SWITCH(op.a, CALL)
 #undef CALL
-            if (op.kind == MOP_G1_REAL) {
+            if (op.kind == MOP_ROT) {
               if (op.acc >= 0) { v = warp_sum(v); if (lane == 0) wacc[op.acc] += v; }
             } else {
               v = sample_sum(v, tb);
               if (lis == 0) gxacc[siw * a.n_inputs + op.idx] += v;
             }
           } break;
-          case MOP_G1_GEN: {
-            const U2 u = load_u(S.coef + op.idx * 8);
-            const U2 ud = dagger(u);
-            float Tm[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-#define CALL(RB) { if (op.acc >= 0) g1_gen_T<RB>(pr, pi, lr, li, Tm); g1_gen<RB>(pr, pi, ud); g1_gen<RB>(lr, li, ud); }
-            RB_SWITCH(op.a, CALL)
+          case MOP_CU3_L:
+          case MOP_CU3_P: {
+            const float2 z = make_float2(0.f, 0.f);
+            Cu3Acc A{z, z, z, z};
+            const Cu3 g = load_cu3(S.coef + op.idx * 8, true);
+            if (op.kind == MOP_CU3_L) {
+              const int rc = op.b;
+#define CALL(RT, RC) cu3_loc_bwd<RT, RC>(ps, ls, g, A)
+              RTC_SWITCH(op.a, CALL)
 #undef CALL
-            if (op.acc >= 0) { const float r = warp_sum8(Tm, lane); if ((lane & 3) == 0) wacc[op.acc + (lane >> 2)] += r; }
-          } break;
-          case MOP_CG1_L: {
-            const U2 u = load_u(S.coef + op.idx * 8);
-            const U2 ud = dagger(u);
-            const int rc = op.b;
-            float Tm[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-#define CALL(RT, RC) { if (op.acc >= 0) cg1_loc_T<RT, RC>(pr, pi, lr, li, Tm); cg1_loc<RT, RC>(pr, pi, ud); cg1_loc<RT, RC>(lr, li, ud); }
-            RTC_SWITCH(op.a, CALL)
-#undef CALL
-            if (op.acc >= 0) { const float r = warp_sum8(Tm, lane); if ((lane & 3) == 0) wacc[op.acc + (lane >> 2)] += r; }
-          } break;
-          case MOP_CG1_P: {
-            float Tm[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-            if (__popc(lis & op.aux) & 1) {
-              const U2 u = load_u(S.coef + op.idx * 8);
-              const U2 ud = dagger(u);
-#define CALL(RB) { if (op.acc >= 0) g1_gen_T<RB>(pr, pi, lr, li, Tm); g1_gen<RB>(pr, pi, ud); g1_gen<RB>(lr, li, ud); }
+            } else if (__popc(lis & op.aux) & 1) {
+#define CALL(RB) cu3_all_bwd<RB>(ps, ls, g, A)
               RB_SWITCH(op.a, CALL)
 #undef CALL
             }
-            if (op.acc >= 0) { const float r = warp_sum8(Tm, lane); if ((lane & 3) == 0) wacc[op.acc + (lane >> 2)] += r; }
+            if (op.acc >= 0) {
+              // theta: Re sum conj(l1)p0 - conj(l0)p1;  phi, lambda: -2 sum Im(conj(l1) p1)
+              const float r = warp_sum4((A.v0.x + A.v0.y) - (A.v1.x + A.v1.y), -2.f * (A.qp.x - A.qp.y),
+                                        -2.f * (A.ql.x - A.ql.y), 0.f, lane);
+              if ((lane & 7) == 0 && (lane >> 3) < 3) wacc[op.acc + (lane >> 3)] += r;
+            }
+          } break;
+          case MOP_ROT5: {
+#define ROT5_STEP(K)                                                                                      \
+            {                                                                                              \
+              const int pos = (op.aux >> (3 * K)) & 7;                                                     \
+              const float2 ab = *reinterpret_cast<const float2*>(S.coef + (op.idx + pos) * 8);             \
+              float v = rot_grad<K>(ps, ls);                                                               \
+              rot<K>(ps, -ab.x, -ab.y); rot<K>(ls, -ab.x, -ab.y);                                          \
+              v = warp_sum(v);                                                                             \
+              if (lane == 0) wacc[op.acc + pos] += v;                                                      \
+            }
+            ROT5_STEP(4) ROT5_STEP(3) ROT5_STEP(2) ROT5_STEP(1) ROT5_STEP(0)
+#undef ROT5_STEP
+          } break;
+          case MOP_ROTX5: {
+#define ROTX5_STEP(K)                                                                                     \
+            {                                                                                              \
+              const int col = (op.idx >> (5 * K)) & 31;                                                    \
+              const float2 ab = rot_coef_x(xrow[col]);                                                     \
+              float v = rot_grad<K>(ps, ls);                                                               \
+              rot<K>(ps, -ab.x, -ab.y); rot<K>(ls, -ab.x, -ab.y);                                          \
+              v = sample_sum(v, tb);                                                                       \
+              if (lis == 0) gxacc[siw * a.n_inputs + col] += v;                                            \
+            }
+            ROTX5_STEP(4) ROTX5_STEP(3) ROTX5_STEP(2) ROTX5_STEP(1) ROTX5_STEP(0)
+#undef ROTX5_STEP
+          } break;
+          case MOP_CU3_CHAIN: {
+#define CHAIN_STEP(K, RT, RC)                                                                              \
+            {                                                                                              \
+              const float2 z = make_float2(0.f, 0.f);                                                      \
+              Cu3Acc A{z, z, z, z};                                                                        \
+              const Cu3 g = load_cu3(S.coef + (op.idx + K) * 8, true);                                     \
+              cu3_loc_bwd<RT, RC>(ps, ls, g, A);                                                           \
+              const float r = warp_sum4((A.v0.x + A.v0.y) - (A.v1.x + A.v1.y), -2.f * (A.qp.x - A.qp.y),   \
+                                        -2.f * (A.ql.x - A.ql.y), 0.f, lane);                              \
+              if ((lane & 7) == 0 && (lane >> 3) < 3) wacc[op.acc + 3 * K + (lane >> 3)] += r;             \
+            }
+            CHAIN_STEP(3, 4, 3)
+            CHAIN_STEP(2, 3, 2)
+            CHAIN_STEP(1, 2, 1)
+            CHAIN_STEP(0, 1, 0)
+#undef CHAIN_STEP
           } break;
           case MOP_DIAG:
           case MOP_DIAG_REG: {
             const DiagDesc* D = S.diags + op.aux;
-            float tot, Sr[kR];
-            signed_sums([&](int j) { return fmaf(lr[j], pi[j], -li[j] * pr[j]); }, tot, Sr);   // Im(conj(lam) psi)
+            float2 tot2, S2[kR];
+            // Im(conj(lam) psi) = lam.re psi.im - lam.im psi.re, kept as the pair (lam.re psi.im, lam.im psi.re)
+            signed_sums2([&](int j) { return __fmul2_rn(ls[j], swp(ps[j])); }, tot2, S2);
 #pragma unroll
             for (int r = 0; r < kR; ++r) {
               const int ai = D->acc_reg[r];
-              if (ai >= 0) { const float v = warp_sum(Sr[r]); if (lane == 0) wacc[ai] += v; }
+              if (ai >= 0) { const float v = warp_sum(S2[r].x - S2[r].y); if (lane == 0) wacc[ai] += v; }
             }
             if (op.kind == MOP_DIAG) {
+              const float tot = tot2.x - tot2.y;
 #pragma unroll
               for (int b = 0; b < 5; ++b) {
                 const int ai = D->acc_lane[b];
                 if (ai >= 0) { const float v = warp_sum(((lis >> b) & 1) ? -tot : tot); if (lane == 0) wacc[ai] += v; }
               }
-              diag_mul<true>(pr, pi, S.big + op.idx * 1024, 32, lane);
-              diag_mul<true>(lr, li, S.big + op.idx * 1024, 32, lane);
+              diag_mul<true, true>(ps, ls, S.big + op.idx * 1024, 32, lane);
             } else {
-              diag_mul<true>(pr, pi, S.small + op.idx * 32, 1, 0);
-              diag_mul<true>(lr, li, S.small + op.idx * 32, 1, 0);
+              diag_mul<true, true>(ps, ls, S.small + op.idx * 32, 1, 0);
             }
           } break;
           case MOP_XCHG:
-            exchange(pr, pi, S.xbuf, S.exchanges + op.idx, lane, true);
-            exchange(lr, li, S.xbuf, S.exchanges + op.idx, lane, true);
+            exchange(ps, S.xbuf, S.exchanges + op.idx, lane, true);
+            exchange(ls, S.xbuf, S.exchanges + op.idx, lane, true);
             break;
           default: break;
         }
+        op = next;
       }
       // ================= input gradients of this warp's samples =================
       __syncwarp();
@@ -557,7 +637,20 @@ __global__ void k_vm_prep(const DevOp* __restrict__ coef_ops, int n_coef, const 
     const DevOp op = coef_ops[i];
     double a[3] = {0, 0, 0};
     for (int k = 0; k < op.nang; ++k) a[k] = (op.src[k] == QNN_SRC_CONST) ? (double)op.value[k] : (double)w[op.src[k]];
-    make_coef<double>(op.kind, a, coef + (size_t)i * QNN_COEF_STRIDE);
+    // row: [al, be, m0, 0, cos l, sin l, cos p, sin p]  (RY rows use al, be only)
+    const double pi = 3.14159265358979323846;
+    double phi = 0.5 * a[0];
+    const double k = rint(phi / pi);
+    phi -= k * pi;
+    float* row = coef + (size_t)i * QNN_COEF_STRIDE;
+    row[0] = (float)(-tan(0.5 * phi));
+    row[1] = (float)sin(phi);
+    row[2] = (((long long)k) & 1LL) ? -1.f : 1.f;
+    row[3] = 0.f;
+    double sl, cl, sp, cp;
+    sincos(a[2], &sl, &cl);
+    sincos(a[1], &sp, &cp);
+    row[4] = (float)cl; row[5] = (float)sl; row[6] = (float)cp; row[7] = (float)sp;
     return;
   }
   const int d = blockIdx.x - coef_blocks;
@@ -585,27 +678,16 @@ __global__ void k_vm_prep(const DevOp* __restrict__ coef_ops, int n_coef, const 
   }
 }
 
-// gw[i] = sum over the gradient slots of weight i, each finished from the CTA partials (fixed order).
+// gw[i] = sum over the gradient slots of weight i of the CTA partials, in a fixed order.
 __global__ void k_vm_finalize(const float* __restrict__ partial, int n_ctas, int n_acc, const GradSlot* __restrict__ slots,
                               const int32_t* __restrict__ slot_ptr, const int32_t* __restrict__ slot_idx,
-                              const float* __restrict__ coef, float* __restrict__ gw) {
+                              float* __restrict__ gw) {
   __shared__ double sred[128];
   const int i = blockIdx.x;
   double acc = 0.0;
   for (int e = slot_ptr[i]; e < slot_ptr[i + 1]; ++e) {
-    const GradSlot s = slots[slot_idx[e]];
-    if (s.kind == 0) {
-      for (int c = threadIdx.x; c < n_ctas; c += blockDim.x) acc += (double)partial[(size_t)c * n_acc + s.acc];
-    } else {
-      const float* G = coef + (size_t)s.coef * QNN_COEF_STRIDE + 8 + 8 * s.angle;
-      for (int c = threadIdx.x; c < n_ctas; c += blockDim.x) {
-        const float* T = partial + (size_t)c * n_acc + s.acc;
-        double v = 0.0;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) v += (double)G[2 * k] * (double)T[2 * k] - (double)G[2 * k + 1] * (double)T[2 * k + 1];
-        acc += 2.0 * v;
-      }
-    }
+    const int ai = slots[slot_idx[e]].acc;
+    for (int c = threadIdx.x; c < n_ctas; c += blockDim.x) acc += (double)partial[(size_t)c * n_acc + ai];
   }
   sred[threadIdx.x] = acc;
   __syncthreads();
@@ -618,9 +700,20 @@ __global__ void k_vm_finalize(const float* __restrict__ partial, int n_ctas, int
 
 size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
 
-constexpr int kFwdThreads = 256, kFwdMinB = 2;
-constexpr int kBwdThreads = 256, kBwdMinB = 1;
 constexpr size_t kSmemMax = 227 * 1024;
+
+struct Variant { int fwd_threads, bwd_threads; };
+Variant variant() {
+  static Variant v = [] {
+    Variant r{512, 384};
+    if (const char* e = getenv("QNN_VM_VARIANT")) {   // tuning knob: "<fwd threads>,<bwd threads>"
+      int a = 0, b = 0;
+      if (sscanf(e, "%d,%d", &a, &b) == 2 && (a == 256 || a == 512) && (b == 256 || b == 384)) { r.fwd_threads = a; r.bwd_threads = b; }
+    }
+    return r;
+  }();
+  return v;
+}
 
 template <typename K>
 int set_smem(K kern, size_t bytes) {
@@ -657,11 +750,12 @@ int launch_prep(const Program& p, const float* w, const VmArgs& a, cudaStream_t 
 
 bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
   if (!p.ok) return false;
-  const size_t sf = smem_bytes(p, c->n_inputs, kFwdThreads / 32, false);
-  const size_t sb = smem_bytes(p, c->n_inputs, kBwdThreads / 32, true);
+  const Variant v = variant();
+  const size_t sf = smem_bytes(p, c->n_inputs, v.fwd_threads / 32, false);
+  const size_t sb = smem_bytes(p, c->n_inputs, v.bwd_threads / 32, true);
   if (sf > kSmemMax || sb > kSmemMax) return false;
-  out->threads = kBwdThreads;
-  out->warps_per_cta = kBwdThreads / 32;
+  out->threads = v.bwd_threads;
+  out->warps_per_cta = v.bwd_threads / 32;
   out->smem_fwd = sf;
   out->smem_bwd = sb;
   const int64_t batches = (B + (32 >> p.tb) - 1) / (32 >> p.tb);
@@ -720,15 +814,20 @@ int forward(const qnn_circuit* c, const Program& p, const Plan& pl, const float*
   a.x = x; a.y = y; a.B = B;
   int rc = launch_prep(p, w, a, st);
   if (rc) return rc;
-  auto kern = k_vm<false, kFwdThreads, kFwdMinB>;
-  if ((rc = set_smem(kern, pl.smem_fwd))) return rc;
-  const int spw = 32 >> p.tb, wpc = kFwdThreads / 32;
+  const Variant v = variant();
+  const int spw = 32 >> p.tb, wpc = v.fwd_threads / 32;
   const int64_t ctas = ((B + spw - 1) / spw + wpc - 1) / wpc;
-  const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(kFwdMinB, kSmemMax / pl.smem_fwd));
-  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, 148 * per_sm));
-  kern<<<grid, kFwdThreads, pl.smem_fwd, st>>>(a);
-  QNN_CUDA_CHECK(cudaGetLastError());
-  return QNN_OK;
+  auto go = [&](auto kern, int minb) -> int {
+    int r = set_smem(kern, pl.smem_fwd);
+    if (r) return r;
+    const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(minb, kSmemMax / pl.smem_fwd));
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, 148 * per_sm));
+    kern<<<grid, v.fwd_threads, pl.smem_fwd, st>>>(a);
+    QNN_CUDA_CHECK(cudaGetLastError());
+    return QNN_OK;
+  };
+  if (v.fwd_threads == 512) return go(k_vm<false, 512, 1>, 1);
+  return go(k_vm<false, 256, 2>, 2);
 }
 
 int backward(const qnn_circuit* c, const Program& p, const Plan& pl, const float* x, const float* w,
@@ -738,12 +837,19 @@ int backward(const qnn_circuit* c, const Program& p, const Plan& pl, const float
   a.x = x; a.gy = gy; a.gx = gx; a.B = B;
   int rc = launch_prep(p, w, a, st);
   if (rc) return rc;
-  auto kern = k_vm<true, kBwdThreads, kBwdMinB>;
-  if ((rc = set_smem(kern, pl.smem_bwd))) return rc;
-  kern<<<pl.grid, kBwdThreads, pl.smem_bwd, st>>>(a);
-  QNN_CUDA_CHECK(cudaGetLastError());
+  const Variant v = variant();
+  auto go = [&](auto kern) -> int {
+    int r = set_smem(kern, pl.smem_bwd);
+    if (r) return r;
+    kern<<<pl.grid, v.bwd_threads, pl.smem_bwd, st>>>(a);
+    QNN_CUDA_CHECK(cudaGetLastError());
+    return QNN_OK;
+  };
+  if (v.bwd_threads == 384) rc = go(k_vm<true, 384, 1>);
+  else rc = go(k_vm<true, 256, 1>);
+  if (rc) return rc;
   if (c->n_weights > 0) {
-    k_vm_finalize<<<c->n_weights, 128, 0, st>>>(a.partial, pl.grid, p.n_acc, p.d_slots, p.d_slot_ptr, p.d_slot_idx, a.coef, gw);
+    k_vm_finalize<<<c->n_weights, 128, 0, st>>>(a.partial, pl.grid, p.n_acc, p.d_slots, p.d_slot_ptr, p.d_slot_idx, gw);
     QNN_CUDA_CHECK(cudaGetLastError());
   }
   return QNN_OK;

@@ -25,14 +25,19 @@ constexpr int kMinQubits = 5, kMaxQubits = 10;
 
 enum MopKind : int32_t {
   MOP_END = 0,
-  MOP_G1_REAL = 1,    // real rotation [[c,-s],[s,c]] on register bit a; coef row idx; acc (1 float)
-  MOP_G1_REAL_X = 2,  // same, angle = x[b, idx] (per sample); gradient goes to gx
-  MOP_G1_GEN = 3,     // general complex 2x2 on register bit a; coef row idx; acc (8 floats: T)
-  MOP_CG1_L = 4,      // controlled 2x2: target register bit a, control register bit b
-  MOP_CG1_P = 5,      // controlled 2x2: target register bit a, control = parity(lane_in_sample & aux)
+  MOP_ROT = 1,        // real rotation RY on register bit a, applied in place as three shears; coef row idx; acc (1)
+  MOP_ROT_X = 2,      // same, angle = x[b, idx] (per sample); gradient goes to gx
+  MOP_CU3_L = 4,      // controlled U3 = diag(1,e^{i phi}) RY(theta) diag(1,e^{i lambda}) on the control=1 pairs:
+                      //   target register bit a, control register bit b; coef row idx; acc (3: theta, phi, lambda)
+  MOP_CU3_P = 5,      // same with control = parity(lane_in_sample & aux)
   MOP_DIAG = 6,       // multiply by diagonal table idx ([j][lane], 1024 entries); desc aux
   MOP_DIAG_REG = 7,   // diagonal that depends on register bits only (32-entry table idx); desc aux
   MOP_XCHG = 8,       // exchange idx
+  // macro-ops: one dispatch for a whole group (the per-op dispatch latency is otherwise comparable to a body)
+  MOP_ROT5 = 9,       // rotations on all five register bits; bit k uses coef row idx + pos_k and accumulator
+                      //   acc + pos_k, pos_k = (aux >> 3k) & 7
+  MOP_ROTX5 = 10,     // per-sample rotations on all five register bits; bit k uses x column (idx >> 5k) & 31
+  MOP_CU3_CHAIN = 11, // CU3_L (t,c) = (1,0), (2,1), (3,2), (4,3) in that order; rows idx..idx+3, accs acc + 3k
 };
 
 struct MicroOp {       // 32 bytes
@@ -58,10 +63,8 @@ struct Exchange {      // byte offsets into the warp's 8 KB buffer; address = ba
   uint32_t wbase[32], woff[32], rbase[32], roff[32];
 };
 
-struct GradSlot {      // how one weight-sourced angle's gradient is obtained from the accumulators
-  int32_t weight;      // index into gw
-  int32_t kind;        // 0: direct (value = acc[a]);  1: 2 Re sum G_k T (acc base a, coef row c, angle k)
-  int32_t acc, coef, angle;
+struct GradSlot {      // gw[weight] += accumulator[acc]  (every gradient is a direct, already-reduced sum)
+  int32_t weight, acc;
 };
 
 struct Program {
@@ -69,7 +72,7 @@ struct Program {
   std::string why_not;           // when !ok: why the VM does not take this circuit (generic path used)
   int n = 0, tb = 0;
   std::vector<MicroOp> ops;      // forward order, MOP_END-terminated
-  std::vector<DevOp> coef_ops;   // recipes for k_prep_coef (mode 1), one per coefficient row
+  std::vector<DevOp> coef_ops;   // recipes (gate kind + angle sources), one per 8-float coefficient row
   std::vector<DiagTerm> terms;
   std::vector<DiagDesc> diags;
   std::vector<Exchange> exchanges;

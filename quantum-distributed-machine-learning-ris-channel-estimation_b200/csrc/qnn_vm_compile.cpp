@@ -18,12 +18,12 @@
 namespace vm {
 namespace {
 
-enum ItemKind { IT_REAL, IT_GEN, IT_RZ, IT_CZ, IT_CNOT, IT_CGEN };
+enum ItemKind { IT_REAL, IT_RZ, IT_CZ, IT_CNOT, IT_CGEN };
 
 struct Item {
   ItemKind kind;
   int w0, w1;          // w0: target of 1q / control of 2q;  w1: target of 2q
-  int gate;            // qnn_gate for coefficient recipes (IT_GEN: RX; IT_CGEN: CU3)
+  int gate;            // qnn_gate for coefficient recipes (IT_REAL: RY; IT_CGEN: CU3)
   int32_t src[3];
   float value[3];
   bool done = false;
@@ -99,11 +99,15 @@ struct Builder {
           it.kind = IT_REAL; it.w0 = o.wire0; it.w1 = -1; it.gate = QNN_RY; it.src[0] = o.src[0]; it.value[0] = o.value[0];
           items.push_back(it);
           break;
-        case QNN_RX:
+        case QNN_RX: {
           if (x_src(o.src[0])) { P->why_not = "RX with an input-sourced angle"; return false; }
-          it.kind = IT_GEN; it.w0 = o.wire0; it.w1 = -1; it.gate = QNN_RX; it.src[0] = o.src[0]; it.value[0] = o.value[0];
-          items.push_back(it);
+          // RX(t) = RZ(-pi/2) RY(t) RZ(pi/2): the constant RZ factors join the merged diagonals
+          Item a = it; a.kind = IT_RZ; a.w0 = o.wire0; a.w1 = -1; a.gate = QNN_RZ; a.value[0] = 1.57079632679489662f;
+          Item b = it; b.kind = IT_REAL; b.w0 = o.wire0; b.w1 = -1; b.gate = QNN_RY; b.src[0] = o.src[0]; b.value[0] = o.value[0];
+          Item d = it; d.kind = IT_RZ; d.w0 = o.wire0; d.w1 = -1; d.gate = QNN_RZ; d.value[0] = -1.57079632679489662f;
+          items.push_back(a); items.push_back(b); items.push_back(d);
           break;
+        }
         case QNN_RZ:
           if (x_src(o.src[0])) { P->why_not = "RZ with an input-sourced angle"; return false; }
           it.kind = IT_RZ; it.w0 = o.wire0; it.w1 = -1; it.gate = QNN_RZ; it.src[0] = o.src[0]; it.value[0] = o.value[0];
@@ -202,7 +206,7 @@ struct Builder {
       if (t.kind == 0 && t.src >= 0) {
         int32_t& a = t.bit0 < kR ? D.acc_reg[t.bit0] : D.acc_lane[t.bit0 - kR];
         if (a < 0) a = P->n_acc++;
-        P->slots.push_back(GradSlot{t.src, 0, a, -1, 0});
+        P->slots.push_back(GradSlot{t.src, a});
       }
       P->terms.push_back(t);
     }
@@ -226,7 +230,6 @@ struct Builder {
       case IT_CZ: return (row_unit(it.w0) && row_unit(it.w1)) ? ST_OK : ST_BLOCKED;
       case IT_CNOT: return pending_on(it.w1) ? ST_NEEDS_FLUSH : ST_OK;
       case IT_REAL:
-      case IT_GEN:
         if (!clean(it.w0) || bit_of(it.w0) >= kR) return ST_BLOCKED;
         return pending_on(it.w0) ? ST_NEEDS_FLUSH : ST_OK;
       case IT_CGEN:
@@ -252,22 +255,16 @@ struct Builder {
         if (pending_on(it.w1)) flush_diag();
         rowmask[it.w1] ^= rowmask[it.w0];
         return true;
-      case IT_REAL:
-      case IT_GEN: {
+      case IT_REAL: {
         if (!clean(it.w0) || bit_of(it.w0) >= kR) return false;
         if (pending_on(it.w0)) flush_diag();
         MicroOp m{};
         m.a = bit_of(it.w0); m.acc = -1;
-        if (it.kind == IT_REAL) {
-          if (it.src[0] < 0 && it.src[0] != QNN_SRC_CONST) {
-            m.kind = MOP_G1_REAL_X; m.idx = -1 - it.src[0];
-          } else {
-            m.kind = MOP_G1_REAL; m.idx = new_coef_row(QNN_RY, it.src, it.value, 1);
-            if (it.src[0] >= 0) { m.acc = P->n_acc++; P->slots.push_back(GradSlot{it.src[0], 0, m.acc, -1, 0}); }
-          }
+        if (it.src[0] < 0 && it.src[0] != QNN_SRC_CONST) {
+          m.kind = MOP_ROT_X; m.idx = -1 - it.src[0];
         } else {
-          m.kind = MOP_G1_GEN; m.idx = new_coef_row(it.gate, it.src, it.value, 1);
-          if (it.src[0] >= 0) { m.acc = P->n_acc; P->n_acc += 8; P->slots.push_back(GradSlot{it.src[0], 1, m.acc, m.idx, 0}); }
+          m.kind = MOP_ROT; m.idx = new_coef_row(QNN_RY, it.src, it.value, 1);
+          if (it.src[0] >= 0) { m.acc = P->n_acc++; P->slots.push_back(GradSlot{it.src[0], m.acc}); }
         }
         P->ops.push_back(m);
         return true;
@@ -278,14 +275,14 @@ struct Builder {
         MicroOp m{};
         m.a = bit_of(it.w1); m.acc = -1;
         const int cb = bit_of(it.w0);
-        if (cb < kR) { m.kind = MOP_CG1_L; m.b = cb; }
-        else { m.kind = MOP_CG1_P; m.aux = 1 << (cb - kR); }
+        if (cb < kR) { m.kind = MOP_CU3_L; m.b = cb; }
+        else { m.kind = MOP_CU3_P; m.aux = 1 << (cb - kR); }
         m.idx = new_coef_row(QNN_CU3, it.src, it.value, 3);
         bool any_w = false;
         for (int k = 0; k < 3; ++k) any_w |= it.src[k] >= 0;
-        if (any_w) {
-          m.acc = P->n_acc; P->n_acc += 8;
-          for (int k = 0; k < 3; ++k) if (it.src[k] >= 0) P->slots.push_back(GradSlot{it.src[k], 1, m.acc, m.idx, k});
+        if (any_w) {   // three direct accumulators: theta, phi, lambda
+          m.acc = P->n_acc; P->n_acc += 3;
+          for (int k = 0; k < 3; ++k) if (it.src[k] >= 0) P->slots.push_back(GradSlot{it.src[k], m.acc + k});
         }
         P->ops.push_back(m);
         return true;
@@ -300,7 +297,7 @@ struct Builder {
     auto add = [&](int w) { if (w >= 0 && std::find(order.begin(), order.end(), w) == order.end()) order.push_back(w); };
     for (size_t i = 0; i < items.size() && (int)order.size() < kR; ++i) {
       if (items[i].done) continue;
-      if (items[i].kind == IT_REAL || items[i].kind == IT_GEN) add(items[i].w0);
+      if (items[i].kind == IT_REAL) add(items[i].w0);
       else if (items[i].kind == IT_CGEN) add(items[i].w1);
     }
     for (size_t i = 0; i < items.size() && (int)order.size() < kR; ++i)
@@ -350,6 +347,56 @@ struct Builder {
     P->ops.push_back(m);
     for (int w = 0; w < n; ++w) rowmask[w] = 1u << new_bit_of_wire[w];
     return true;
+  }
+
+  // Peephole: groups that layered circuits produce become one macro-op (one dispatch instead of 4-5).
+  void fuse_groups() {
+    std::vector<MicroOp> out;
+    const std::vector<MicroOp>& in = P->ops;
+    for (size_t i = 0; i < in.size();) {
+      auto distinct_bits = [&](int kind, bool need_acc) {
+        if (i + 5 > in.size()) return false;
+        uint32_t seen = 0;
+        for (int k = 0; k < 5; ++k) {
+          const MicroOp& m = in[i + k];
+          if (m.kind != kind || ((seen >> m.a) & 1u)) return false;
+          if (need_acc && (m.acc != in[i].acc + k || m.idx != in[i].idx + k)) return false;
+          seen |= 1u << m.a;
+        }
+        return seen == 31u;
+      };
+      if (distinct_bits(MOP_ROT, true)) {
+        MicroOp m{};
+        m.kind = MOP_ROT5; m.idx = in[i].idx; m.acc = in[i].acc;
+        for (int k = 0; k < 5; ++k) m.aux |= k << (3 * in[i + k].a);
+        out.push_back(m);
+        i += 5;
+        continue;
+      }
+      if (distinct_bits(MOP_ROT_X, false)) {
+        MicroOp m{};
+        m.kind = MOP_ROTX5; m.acc = -1;
+        for (int k = 0; k < 5; ++k) m.idx |= in[i + k].idx << (5 * in[i + k].a);
+        out.push_back(m);
+        i += 5;
+        continue;
+      }
+      bool chain = i + 4 <= in.size();
+      for (int k = 0; chain && k < 4; ++k) {
+        const MicroOp& m = in[i + k];
+        chain = m.kind == MOP_CU3_L && m.a == k + 1 && m.b == k && m.idx == in[i].idx + k && in[i].acc >= 0 &&
+                m.acc == in[i].acc + 3 * k;
+      }
+      if (chain) {
+        MicroOp m{};
+        m.kind = MOP_CU3_CHAIN; m.idx = in[i].idx; m.acc = in[i].acc;
+        out.push_back(m);
+        i += 4;
+        continue;
+      }
+      out.push_back(in[i++]);
+    }
+    P->ops.swap(out);
   }
 
   bool all_clean() const {
@@ -431,6 +478,7 @@ struct Builder {
       if (!emit_exchange(bits)) return false;
     }
     for (int w = 0; w < n; ++w) P->final_bit_of_wire[w] = bit_of(w);
+    fuse_groups();
     MicroOp e{};
     e.kind = MOP_END; e.acc = -1;
     P->ops.push_back(e);
@@ -446,9 +494,13 @@ static double program_cost(const Program& p) {
   double cost = 0;
   for (const MicroOp& m : p.ops) {
     switch (m.kind) {
-      case MOP_G1_REAL: case MOP_G1_REAL_X: case MOP_CG1_L: case MOP_DIAG_REG: cost += 4; break;
-      case MOP_G1_GEN: case MOP_CG1_P: cost += 8; break;
-      case MOP_DIAG: cost += 4.5; break;
+      case MOP_ROT: case MOP_ROT_X: cost += 1.5; break;
+      case MOP_ROT5: case MOP_ROTX5: cost += 7.0; break;
+      case MOP_CU3_CHAIN: cost += 11.0; break;
+      case MOP_CU3_L: cost += 3.0; break;
+      case MOP_CU3_P: cost += 6.0; break;
+      case MOP_DIAG_REG: cost += 5.0; break;
+      case MOP_DIAG: cost += 6.0; break;
       case MOP_XCHG: cost += 4.6; break;
       default: break;
     }
@@ -479,6 +531,7 @@ void compile(const qnn_circuit* c, Program* out) {
 
 std::string describe(const Program& p) {
   std::ostringstream o;
+  o.precision(9);
   o << "{\"ok\": " << (p.ok ? "true" : "false") << ", \"why_not\": \"" << p.why_not << "\"";
   if (!p.ok) { o << "}"; return o.str(); }
   o << ", \"n\": " << p.n << ", \"tb\": " << p.tb << ", \"n_acc\": " << p.n_acc;
@@ -530,7 +583,7 @@ std::string describe(const Program& p) {
   o << "], \"slots\": [";
   for (size_t i = 0; i < p.slots.size(); ++i) {
     const GradSlot& s = p.slots[i];
-    o << (i ? ", " : "") << "[" << s.weight << ", " << s.kind << ", " << s.acc << ", " << s.coef << ", " << s.angle << "]";
+    o << (i ? ", " : "") << "[" << s.weight << ", " << s.acc << "]";
   }
   o << "]}";
   return o.str();

@@ -9,7 +9,7 @@ import numpy as np
 
 SRC_CONST = -(2 ** 31)
 RX, RY, RZ, U3, CNOT, CZ, CU3 = range(7)
-(MOP_END, MOP_G1_REAL, MOP_G1_REAL_X, MOP_G1_GEN, MOP_CG1_L, MOP_CG1_P, MOP_DIAG, MOP_DIAG_REG, MOP_XCHG) = range(9)
+(MOP_END, MOP_G1_REAL, MOP_G1_REAL_X, MOP_G1_GEN, MOP_CG1_L, MOP_CG1_P, MOP_DIAG, MOP_DIAG_REG, MOP_XCHG, MOP_ROT5, MOP_ROTX5, MOP_CU3_CHAIN) = range(12)
 
 
 def _angle(src, value, w):
@@ -85,6 +85,23 @@ def emulate_forward(desc, x, w):
                 par = np.array([bin(int(v) & aux).count("1") & 1 for v in lis], bool)
                 _apply_reg(state, U, a, lane_mask=par)
                 stats["cg_p"] += 1
+        elif kind == MOP_ROT5:
+            for k in range(5):
+                co = desc["coef_ops"][idx + ((aux >> (3 * k)) & 7)]
+                _apply_reg(state, _matrix(co["kind"], [_angle(s_, v_, w) for s_, v_ in zip(co["src"], co["value"])]), k)
+            stats["g1"] += 5
+        elif kind == MOP_ROTX5:
+            for k in range(5):
+                col = (idx >> (5 * k)) & 31
+                for s in range(spw):
+                    _apply_reg(state, _matrix(RY, [x[s, col]]), k, lane_mask=(samp == s))
+            stats["g1"] += 5
+        elif kind == MOP_CU3_CHAIN:
+            for k in range(4):
+                co = desc["coef_ops"][idx + k]
+                U = _matrix(U3, [_angle(s_, v_, w) for s_, v_ in zip(co["src"], co["value"])])
+                _apply_reg(state, U, k + 1, ctrl_rbit=k)
+            stats["cg_l"] += 4
         elif kind in (MOP_DIAG, MOP_DIAG_REG):
             D = desc["diags"][aux]
             assert bool(D["is_reg"]) == (kind == MOP_DIAG_REG)
