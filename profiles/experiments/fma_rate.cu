@@ -60,6 +60,20 @@ __global__ void __launch_bounds__(THREADS) k(float* out, const float* in, int it
           a[2 * i] = __ffma2_rn(ns2, a1, __fmul2_rn(c2, a0));
           a[2 * i + 1] = __ffma2_rn(s2, a0, __fmul2_rn(c2, a1));
         }
+      } else if (MODE == 8) {  // in-place 3-shear rotation on bit 0: 3 packed per pair
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          a[2 * i] = __ffma2_rn(c2, a[2 * i + 1], a[2 * i]);
+          a[2 * i + 1] = __ffma2_rn(s2, a[2 * i], a[2 * i + 1]);
+          a[2 * i] = __ffma2_rn(c2, a[2 * i + 1], a[2 * i]);
+        }
+      } else if (MODE == 9) {  // in-place 3-shear rotation on bit 4
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          a[i] = __ffma2_rn(c2, a[i + 16], a[i]);
+          a[i + 16] = __ffma2_rn(s2, a[i], a[i + 16]);
+          a[i] = __ffma2_rn(c2, a[i + 16], a[i]);
+        }
       } else if (MODE == 7) {  // packed general complex 2x2 on bit 0 (first row only + second row): 8 packed + 4 swaps / pair
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
@@ -89,7 +103,8 @@ void run(const char* name, float* d_out, float* d_in, int ctas_per_sm) {
   k<MODE, THREADS><<<grid, THREADS>>>(d_out, d_in, iters, 0.999f, 1e-4f);
   cudaEventRecord(e1); cudaEventSynchronize(e1);
   float ms; cudaEventElapsedTime(&ms, e0, e1);
-  const double instr = (double)grid * (THREADS / 32) * iters * 128.0;   // FMA-pipe warp instructions
+  const double per_iter = (MODE == 8 || MODE == 9) ? 96.0 : 128.0;     // scalar-equivalent FMA-pipe instructions
+  const double instr = (double)grid * (THREADS / 32) * iters * per_iter;
   const double per_clk_smsp = instr / (ms * 1e-3 * 1.965e9) / (148 * 4);
   printf("%-34s threads=%4d ctas/sm=%d: %.3f ms, %.3f FMA-pipe instr/clk/SMSP\n", name, THREADS, ctas_per_sm, ms, per_clk_smsp);
 }
@@ -111,5 +126,10 @@ int main() {
   run<6, 512>("packed rotation bit0", d_out, d_in, 1);
   run<6, 128>("packed rotation bit0", d_out, d_in, 1);
   run<7, 256>("packed general 2x2 (256 scalar-eq)", d_out, d_in, 2);
+  run<8, 256>("packed shear rot bit0", d_out, d_in, 2);
+  run<8, 512>("packed shear rot bit0", d_out, d_in, 1);
+  run<8, 256>("packed shear rot bit0", d_out, d_in, 1);
+  run<9, 256>("packed shear rot bit4", d_out, d_in, 2);
+  run<9, 128>("packed shear rot bit4", d_out, d_in, 1);
   return 0;
 }

@@ -34,6 +34,7 @@ struct VmArgs {
   const float2* big; int n_big;             // [n_big][1024]
   const float2* small; int n_small;         // [n_small][32]
   int n, tb, n_inputs, n_acc;
+  unsigned skip_mask;                       // experiments only (QNN_VM_SKIP): micro-op kinds to skip
   int8_t wire_of_bit[16];                   // final (measurement) layout
   const float* x; float* y;                 // forward
   const float* gy; float* gx; float* partial;  // backward; partial [grid][n_acc]
@@ -90,13 +91,16 @@ __device__ __forceinline__ void rot_grad_acc(float2& v0, float2& v1, float2 p0, 
 }
 template <int RB>
 __device__ __forceinline__ float rot_grad(const float2 (&ps)[NA], const float2 (&ls)[NA]) {
-  float2 v0 = make_float2(0.f, 0.f), v1 = make_float2(0.f, 0.f);
+  const float2 z = make_float2(0.f, 0.f);
+  float2 v0[4] = {z, z, z, z}, v1[4] = {z, z, z, z};   // four independent chains: the FMA latency is exposed otherwise
 #pragma unroll
   for (int i = 0; i < NA / 2; ++i) {
     const int j0 = pair_lo<RB>(i), j1 = j0 | (1 << RB);
-    rot_grad_acc(v0, v1, ps[j0], ps[j1], ls[j0], ls[j1]);
+    rot_grad_acc(v0[i & 3], v1[i & 3], ps[j0], ps[j1], ls[j0], ls[j1]);
   }
-  return (v0.x + v0.y) - (v1.x + v1.y);
+  const float2 a = __fadd2_rn(__fadd2_rn(v0[0], v0[1]), __fadd2_rn(v0[2], v0[3]));
+  const float2 b = __fadd2_rn(__fadd2_rn(v1[0], v1[1]), __fadd2_rn(v1[2], v1[3]));
+  return (a.x + a.y) - (b.x + b.y);
 }
 
 // a <- e * a for a unit complex e = (er, ei), in place: er*a + (-ei, ei) (.) swap(a)
@@ -108,8 +112,7 @@ struct Cu3 {
   float al, be, m0, elr, epr;
   float2 eli, epi;     // (-im, +im) of m0*e^{i lambda} and e^{i phi}
 };
-__device__ __forceinline__ Cu3 load_cu3(const float* c, bool inverse) {
-  const float4 a = *reinterpret_cast<const float4*>(c), b = *reinterpret_cast<const float4*>(c + 4);
+__device__ __forceinline__ Cu3 make_cu3(float4 a, float4 b, bool inverse) {
   Cu3 g;
   g.m0 = a.z;
   if (!inverse) {
@@ -128,6 +131,9 @@ __device__ __forceinline__ void cu3_pair(const Cu3& g, float2& a0, float2& a1) {
   a1 = fma2(g.be, a0, a1);
   a0 = fma2(g.al, a1, a0);
   a1 = cmul(g.epr, g.epi, a1);
+}
+__device__ __forceinline__ Cu3 load_cu3(const float* c, bool inverse) {
+  return make_cu3(*reinterpret_cast<const float4*>(c), *reinterpret_cast<const float4*>(c + 4), inverse);
 }
 // Reverse step on one pair, for psi (p) and lam (l) together, g = load_cu3(.., inverse=true).
 // Accumulates (as packed pairs, finished by the caller): q_phi, v_theta0/1, q_lambda.
@@ -231,6 +237,34 @@ __device__ __forceinline__ float sample_sum(float v, int tb) {   // over the 2^t
   for (int b = 0; b < tb; ++b) v += __shfl_xor_sync(0xffffffffu, v, 1 << b);
   return v;
 }
+// 16 values summed over the warp with the halving butterfly (8+4+2+1+1 = 16 shuffles, depth 5):
+// afterwards lane l holds component l >> 1, fully reduced.
+__device__ __forceinline__ float warp_sum16(const float (&t)[16], int lane) {
+  float k8[8], k4[4], k2[2];
+  {
+    const bool up = lane & 16;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) k8[i] = (up ? t[8 + i] : t[i]) + __shfl_xor_sync(0xffffffffu, up ? t[i] : t[8 + i], 16);
+  }
+  {
+    const bool up = lane & 8;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) k4[i] = (up ? k8[4 + i] : k8[i]) + __shfl_xor_sync(0xffffffffu, up ? k8[i] : k8[4 + i], 8);
+  }
+  {
+    const bool up = lane & 4;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) k2[i] = (up ? k4[2 + i] : k4[i]) + __shfl_xor_sync(0xffffffffu, up ? k4[i] : k4[2 + i], 4);
+  }
+  float k;
+  {
+    const bool up = lane & 2;
+    k = (up ? k2[1] : k2[0]) + __shfl_xor_sync(0xffffffffu, up ? k2[0] : k2[1], 2);
+  }
+  k += __shfl_xor_sync(0xffffffffu, k, 1);
+  return k;
+}
+
 // 4 values summed over the warp with the halving butterfly: afterwards lane l holds component
 // 2*bit4 + bit3 of l, fully reduced (9 shuffles instead of 20).
 __device__ __forceinline__ float warp_sum4(float t0, float t1, float t2, float t3, int lane) {
@@ -309,7 +343,8 @@ struct Smem {
   float2* big;        // [n_big][1024]
   float2* small;      // [n_small][32]
   float* wacc;        // [warps][n_acc]        (backward)
-  float* gxacc;       // [warps][32 * n_inputs / ... ]  = [warps][spw * n_inputs]
+  float* gxacc;       // [warps][spw * n_inputs]
+  float2* xcoef;      // [warps][spw * n_inputs]: shear coefficients of RY(x[b, col]), made once per warp-batch
   uint32_t xbuf;      // shared address of this warp's 8 KB exchange buffer
 };
 
@@ -322,6 +357,7 @@ size_t smem_bytes(const Program& p, int n_inputs, int warps, bool bwd) {
   b += p.coef_ops.size() * 8 * sizeof(float);
   b += (size_t)p.n_big_tables * 1024 * sizeof(float2);
   b += (size_t)p.n_small_tables * 32 * sizeof(float2);
+  b += (size_t)warps * (32 >> p.tb) * std::max(n_inputs, 1) * sizeof(float2);
   if (bwd) {
     b += (size_t)warps * std::max(p.n_acc, 1) * sizeof(float);
     b += (size_t)warps * (32 >> p.tb) * std::max(n_inputs, 1) * sizeof(float);
@@ -351,6 +387,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
     S.coef = reinterpret_cast<float*>(take((size_t)a.n_coef * 8 * sizeof(float)));
     S.big = reinterpret_cast<float2*>(take((size_t)a.n_big * 1024 * sizeof(float2)));
     S.small = reinterpret_cast<float2*>(take((size_t)a.n_small * 32 * sizeof(float2)));
+    S.xcoef = reinterpret_cast<float2*>(take((size_t)WARPS * spw * max(a.n_inputs, 1) * sizeof(float2)));
     if (BWD) {
       S.wacc = reinterpret_cast<float*>(take((size_t)WARPS * max(a.n_acc, 1) * sizeof(float)));
       S.gxacc = reinterpret_cast<float*>(take((size_t)WARPS * spw * max(a.n_inputs, 1) * sizeof(float)));
@@ -377,76 +414,80 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
   float* const wacc = BWD ? S.wacc + (size_t)warp * max(a.n_acc, 1) : nullptr;
   float* const gxacc = BWD ? S.gxacc + (size_t)warp * spw * max(a.n_inputs, 1) : nullptr;
 
+  float2* const xcoef = S.xcoef + (size_t)warp * spw * max(a.n_inputs, 1);
   float2 ps[NA];
   const long long n_batches = (a.B + spw - 1) / spw;
   for (long long wb = (long long)blockIdx.x * WARPS + warp; wb < n_batches; wb += (long long)gridDim.x * WARPS) {
     const long long bs = wb * spw + siw;
     const bool active = bs < a.B;
-    const float* xrow = a.x + (size_t)(active ? bs : a.B - 1) * a.n_inputs;
+
+    // shear coefficients of the per-sample rotations RY(x[b, col]): each (sample, column) once per batch
+    __syncwarp();
+    for (int i = lane; i < spw * a.n_inputs; i += 32) {
+      const long long bb = wb * spw + i / a.n_inputs;
+      xcoef[i] = rot_coef_x(bb < a.B ? a.x[(size_t)bb * a.n_inputs + (i % a.n_inputs)] : 0.f);
+    }
+    __syncwarp();
+    const float2* const xc = xcoef + siw * a.n_inputs;
 
 #pragma unroll
     for (int j = 0; j < NA; ++j) ps[j] = make_float2(0.f, 0.f);
     ps[0].x = lis == 0 ? 1.f : 0.f;
 
     // ================= forward program =================
+    // One jump per micro-op (handler id = kind and register bits); the next op and its coefficient row
+    // are fetched while the current body runs, so the dispatch latency overlaps with arithmetic.
     {
       MicroOp op = S.ops[0];
-      for (int pc = 0; op.kind != MOP_END; ++pc) {
-        const MicroOp next = S.ops[pc + 1];    // fetched early: hides the shared-memory latency of the dispatch
-        switch (op.kind) {
-          case MOP_ROT: {
-            const float2 ab = *reinterpret_cast<const float2*>(S.coef + op.idx * 8);
-#define CALL(RB) rot<RB>(ps, ab.x, ab.y)
-            RB_SWITCH(op.a, CALL)
-#undef CALL
-          } break;
-          case MOP_ROT_X: {
-            const float2 ab = rot_coef_x(xrow[op.idx]);
-#define CALL(RB) rot<RB>(ps, ab.x, ab.y)
-            RB_SWITCH(op.a, CALL)
-#undef CALL
-          } break;
-          case MOP_CU3_L: {
-            const Cu3 g = load_cu3(S.coef + op.idx * 8, false);
-            const int rc = op.b;
-#define CALL(RT, RC) cu3_loc<RT, RC>(ps, g)
-            RTC_SWITCH(op.a, CALL)
-#undef CALL
-          } break;
-          case MOP_CU3_P: {
-            if (__popc(lis & op.aux) & 1) {
-              const Cu3 g = load_cu3(S.coef + op.idx * 8, false);
-#define CALL(RB) cu3_all<RB>(ps, g)
-              RB_SWITCH(op.a, CALL)
-#undef CALL
-            }
-          } break;
-          case MOP_ROT5: {
+      float4 cfa = *reinterpret_cast<const float4*>(S.coef + op.pad1 * 8);
+      for (int pc = 0; op.pad0 != H_END; ++pc) {
+        const MicroOp next = S.ops[pc + 1];
+        const float4 ncfa = *reinterpret_cast<const float4*>(S.coef + next.pad1 * 8);
+        if ((a.skip_mask >> op.kind) & 1u) { op = next; cfa = ncfa; continue; }
+        switch (op.pad0) {
+#define H_CASE_ROT(RB) case H_ROT + RB: rot<RB>(ps, cfa.x, cfa.y); break;
+          H_CASE_ROT(0) H_CASE_ROT(1) H_CASE_ROT(2) H_CASE_ROT(3) H_CASE_ROT(4)
+#undef H_CASE_ROT
+#define H_CASE_ROTX(RB) case H_ROTX + RB: { const float2 ab = xc[op.idx]; rot<RB>(ps, ab.x, ab.y); } break;
+          H_CASE_ROTX(0) H_CASE_ROTX(1) H_CASE_ROTX(2) H_CASE_ROTX(3) H_CASE_ROTX(4)
+#undef H_CASE_ROTX
+#define H_CASE_CU3L(RT, RC) case H_CU3L + RT * 4 + (RC < RT ? RC : RC - 1): { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_loc<RT, RC>(ps, g); } break;
+          H_CASE_CU3L(0, 1) H_CASE_CU3L(0, 2) H_CASE_CU3L(0, 3) H_CASE_CU3L(0, 4)
+          H_CASE_CU3L(1, 0) H_CASE_CU3L(1, 2) H_CASE_CU3L(1, 3) H_CASE_CU3L(1, 4)
+          H_CASE_CU3L(2, 0) H_CASE_CU3L(2, 1) H_CASE_CU3L(2, 3) H_CASE_CU3L(2, 4)
+          H_CASE_CU3L(3, 0) H_CASE_CU3L(3, 1) H_CASE_CU3L(3, 2) H_CASE_CU3L(3, 4)
+          H_CASE_CU3L(4, 0) H_CASE_CU3L(4, 1) H_CASE_CU3L(4, 2) H_CASE_CU3L(4, 3)
+#undef H_CASE_CU3L
+#define H_CASE_CU3P(RB) case H_CU3P + RB: if (__popc(lis & op.aux) & 1) { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_all<RB>(ps, g); } break;
+          H_CASE_CU3P(0) H_CASE_CU3P(1) H_CASE_CU3P(2) H_CASE_CU3P(3) H_CASE_CU3P(4)
+#undef H_CASE_CU3P
+          case H_ROT5: {
             float2 ab[5];
 #pragma unroll
             for (int k = 0; k < 5; ++k) ab[k] = *reinterpret_cast<const float2*>(S.coef + (op.idx + ((op.aux >> (3 * k)) & 7)) * 8);
             rot<0>(ps, ab[0].x, ab[0].y); rot<1>(ps, ab[1].x, ab[1].y); rot<2>(ps, ab[2].x, ab[2].y);
             rot<3>(ps, ab[3].x, ab[3].y); rot<4>(ps, ab[4].x, ab[4].y);
           } break;
-          case MOP_ROTX5: {
+          case H_ROTX5: {
             float2 ab[5];
 #pragma unroll
-            for (int k = 0; k < 5; ++k) ab[k] = rot_coef_x(xrow[(op.idx >> (5 * k)) & 31]);
+            for (int k = 0; k < 5; ++k) ab[k] = xc[(op.idx >> (5 * k)) & 31];
             rot<0>(ps, ab[0].x, ab[0].y); rot<1>(ps, ab[1].x, ab[1].y); rot<2>(ps, ab[2].x, ab[2].y);
             rot<3>(ps, ab[3].x, ab[3].y); rot<4>(ps, ab[4].x, ab[4].y);
           } break;
-          case MOP_CU3_CHAIN: {
-            { const Cu3 g = load_cu3(S.coef + (op.idx + 0) * 8, false); cu3_loc<1, 0>(ps, g); }
+          case H_CHAIN: {
+            { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_loc<1, 0>(ps, g); }
             { const Cu3 g = load_cu3(S.coef + (op.idx + 1) * 8, false); cu3_loc<2, 1>(ps, g); }
             { const Cu3 g = load_cu3(S.coef + (op.idx + 2) * 8, false); cu3_loc<3, 2>(ps, g); }
             { const Cu3 g = load_cu3(S.coef + (op.idx + 3) * 8, false); cu3_loc<4, 3>(ps, g); }
           } break;
-          case MOP_DIAG: diag_mul<false, false>(ps, ps, S.big + op.idx * 1024, 32, lane); break;
-          case MOP_DIAG_REG: diag_mul<false, false>(ps, ps, S.small + op.idx * 32, 1, 0); break;
-          case MOP_XCHG: exchange(ps, S.xbuf, S.exchanges + op.idx, lane, false); break;
+          case H_DIAG: diag_mul<false, false>(ps, ps, S.big + op.idx * 1024, 32, lane); break;
+          case H_DIAGR: diag_mul<false, false>(ps, ps, S.small + op.idx * 32, 1, 0); break;
+          case H_XCHG: exchange(ps, S.xbuf, S.exchanges + op.idx, lane, false); break;
           default: break;
         }
         op = next;
+        cfa = ncfa;
       }
     }
 
@@ -490,63 +531,60 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
       }
       // ================= reverse program =================
       MicroOp op = S.ops[a.n_ops - 2];
+      float4 cfa = *reinterpret_cast<const float4*>(S.coef + op.pad1 * 8);
       for (int pc = a.n_ops - 2; pc >= 0; --pc) {
         const MicroOp next = S.ops[pc > 0 ? pc - 1 : 0];
-        switch (op.kind) {
-          case MOP_ROT:
-          case MOP_ROT_X: {
-            const float2 ab = op.kind == MOP_ROT ? *reinterpret_cast<const float2*>(S.coef + op.idx * 8) : rot_coef_x(xrow[op.idx]);
-            float v = 0.f;
-#define CALL(RB) { v = rot_grad<RB>(ps, ls); rot<RB>(ps, -ab.x, -ab.y); rot<RB>(ls, -ab.x, -ab.y); }
-            RB_SWITCH(op.a, CALL)
-#undef CALL
-            if (op.kind == MOP_ROT) {
-              if (op.acc >= 0) { v = warp_sum(v); if (lane == 0) wacc[op.acc] += v; }
-            } else {
-              v = sample_sum(v, tb);
-              if (lis == 0) gxacc[siw * a.n_inputs + op.idx] += v;
+        const float4 ncfa = *reinterpret_cast<const float4*>(S.coef + next.pad1 * 8);
+        if ((a.skip_mask >> op.kind) & 1u) { op = next; cfa = ncfa; continue; }
+        switch (op.pad0) {
+#define H_CASE_ROT(RB) case H_ROT + RB: { float v = rot_grad<RB>(ps, ls); rot<RB>(ps, -cfa.x, -cfa.y); rot<RB>(ls, -cfa.x, -cfa.y); \
+            if (op.acc >= 0) { v = warp_sum(v); if (lane == 0) wacc[op.acc] += v; } } break;
+          H_CASE_ROT(0) H_CASE_ROT(1) H_CASE_ROT(2) H_CASE_ROT(3) H_CASE_ROT(4)
+#undef H_CASE_ROT
+#define H_CASE_ROTX(RB) case H_ROTX + RB: { const float2 ab = xc[op.idx]; float v = rot_grad<RB>(ps, ls); rot<RB>(ps, -ab.x, -ab.y); rot<RB>(ls, -ab.x, -ab.y); \
+            v = sample_sum(v, tb); if (lis == 0) gxacc[siw * a.n_inputs + op.idx] += v; } break;
+          H_CASE_ROTX(0) H_CASE_ROTX(1) H_CASE_ROTX(2) H_CASE_ROTX(3) H_CASE_ROTX(4)
+#undef H_CASE_ROTX
+#define CU3_REDUCE(A, ACC)                                                                                  \
+            if ((ACC) >= 0) {                                                                               \
+              const float r = warp_sum4((A.v0.x + A.v0.y) - (A.v1.x + A.v1.y), -2.f * (A.qp.x - A.qp.y),    \
+                                        -2.f * (A.ql.x - A.ql.y), 0.f, lane);                               \
+              if ((lane & 7) == 0 && (lane >> 3) < 3) wacc[(ACC) + (lane >> 3)] += r;                       \
             }
-          } break;
-          case MOP_CU3_L:
-          case MOP_CU3_P: {
-            const float2 z = make_float2(0.f, 0.f);
-            Cu3Acc A{z, z, z, z};
-            const Cu3 g = load_cu3(S.coef + op.idx * 8, true);
-            if (op.kind == MOP_CU3_L) {
-              const int rc = op.b;
-#define CALL(RT, RC) cu3_loc_bwd<RT, RC>(ps, ls, g, A)
-              RTC_SWITCH(op.a, CALL)
-#undef CALL
-            } else if (__popc(lis & op.aux) & 1) {
-#define CALL(RB) cu3_all_bwd<RB>(ps, ls, g, A)
-              RB_SWITCH(op.a, CALL)
-#undef CALL
-            }
-            if (op.acc >= 0) {
-              // theta: Re sum conj(l1)p0 - conj(l0)p1;  phi, lambda: -2 sum Im(conj(l1) p1)
-              const float r = warp_sum4((A.v0.x + A.v0.y) - (A.v1.x + A.v1.y), -2.f * (A.qp.x - A.qp.y),
-                                        -2.f * (A.ql.x - A.ql.y), 0.f, lane);
-              if ((lane & 7) == 0 && (lane >> 3) < 3) wacc[op.acc + (lane >> 3)] += r;
-            }
-          } break;
-          case MOP_ROT5: {
-#define ROT5_STEP(K)                                                                                      \
+#define H_CASE_CU3L(RT, RC) case H_CU3L + RT * 4 + (RC < RT ? RC : RC - 1): { const float2 z = make_float2(0.f, 0.f); Cu3Acc A{z, z, z, z}; \
+            const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), true); cu3_loc_bwd<RT, RC>(ps, ls, g, A); CU3_REDUCE(A, op.acc) } break;
+          H_CASE_CU3L(0, 1) H_CASE_CU3L(0, 2) H_CASE_CU3L(0, 3) H_CASE_CU3L(0, 4)
+          H_CASE_CU3L(1, 0) H_CASE_CU3L(1, 2) H_CASE_CU3L(1, 3) H_CASE_CU3L(1, 4)
+          H_CASE_CU3L(2, 0) H_CASE_CU3L(2, 1) H_CASE_CU3L(2, 3) H_CASE_CU3L(2, 4)
+          H_CASE_CU3L(3, 0) H_CASE_CU3L(3, 1) H_CASE_CU3L(3, 2) H_CASE_CU3L(3, 4)
+          H_CASE_CU3L(4, 0) H_CASE_CU3L(4, 1) H_CASE_CU3L(4, 2) H_CASE_CU3L(4, 3)
+#undef H_CASE_CU3L
+#define H_CASE_CU3P(RB) case H_CU3P + RB: { const float2 z = make_float2(0.f, 0.f); Cu3Acc A{z, z, z, z}; \
+            if (__popc(lis & op.aux) & 1) { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), true); cu3_all_bwd<RB>(ps, ls, g, A); } \
+            CU3_REDUCE(A, op.acc) } break;
+          H_CASE_CU3P(0) H_CASE_CU3P(1) H_CASE_CU3P(2) H_CASE_CU3P(3) H_CASE_CU3P(4)
+#undef H_CASE_CU3P
+          case H_ROT5: {
+            float v[5];
+#define ROT5_STEP(K)                                                                                       \
             {                                                                                              \
               const int pos = (op.aux >> (3 * K)) & 7;                                                     \
               const float2 ab = *reinterpret_cast<const float2*>(S.coef + (op.idx + pos) * 8);             \
-              float v = rot_grad<K>(ps, ls);                                                               \
+              v[K] = rot_grad<K>(ps, ls);                                                                  \
               rot<K>(ps, -ab.x, -ab.y); rot<K>(ls, -ab.x, -ab.y);                                          \
-              v = warp_sum(v);                                                                             \
-              if (lane == 0) wacc[op.acc + pos] += v;                                                      \
             }
             ROT5_STEP(4) ROT5_STEP(3) ROT5_STEP(2) ROT5_STEP(1) ROT5_STEP(0)
 #undef ROT5_STEP
+            // five sums in one halving butterfly: lane 8k' ... holds component (lane >> 2)
+            const float t8[16] = {v[0], v[1], v[2], v[3], v[4], 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            const float r = warp_sum16(t8, lane);
+            if ((lane & 1) == 0 && (lane >> 1) < 5) wacc[op.acc + ((op.aux >> (3 * (lane >> 1))) & 7)] += r;
           } break;
-          case MOP_ROTX5: {
-#define ROTX5_STEP(K)                                                                                     \
+          case H_ROTX5: {
+#define ROTX5_STEP(K)                                                                                      \
             {                                                                                              \
               const int col = (op.idx >> (5 * K)) & 31;                                                    \
-              const float2 ab = rot_coef_x(xrow[col]);                                                     \
+              const float2 ab = xc[col];                                                                   \
               float v = rot_grad<K>(ps, ls);                                                               \
               rot<K>(ps, -ab.x, -ab.y); rot<K>(ls, -ab.x, -ab.y);                                          \
               v = sample_sum(v, tb);                                                                       \
@@ -555,16 +593,14 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
             ROTX5_STEP(4) ROTX5_STEP(3) ROTX5_STEP(2) ROTX5_STEP(1) ROTX5_STEP(0)
 #undef ROTX5_STEP
           } break;
-          case MOP_CU3_CHAIN: {
+          case H_CHAIN: {
 #define CHAIN_STEP(K, RT, RC)                                                                              \
             {                                                                                              \
               const float2 z = make_float2(0.f, 0.f);                                                      \
               Cu3Acc A{z, z, z, z};                                                                        \
               const Cu3 g = load_cu3(S.coef + (op.idx + K) * 8, true);                                     \
               cu3_loc_bwd<RT, RC>(ps, ls, g, A);                                                           \
-              const float r = warp_sum4((A.v0.x + A.v0.y) - (A.v1.x + A.v1.y), -2.f * (A.qp.x - A.qp.y),   \
-                                        -2.f * (A.ql.x - A.ql.y), 0.f, lane);                              \
-              if ((lane & 7) == 0 && (lane >> 3) < 3) wacc[op.acc + 3 * K + (lane >> 3)] += r;             \
+              CU3_REDUCE(A, op.acc + 3 * K)                                                                \
             }
             CHAIN_STEP(3, 4, 3)
             CHAIN_STEP(2, 3, 2)
@@ -572,36 +608,39 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
             CHAIN_STEP(0, 1, 0)
 #undef CHAIN_STEP
           } break;
-          case MOP_DIAG:
-          case MOP_DIAG_REG: {
+#undef CU3_REDUCE
+          case H_DIAG:
+          case H_DIAGR: {
             const DiagDesc* D = S.diags + op.aux;
             float2 tot2, S2[kR];
             // Im(conj(lam) psi) = lam.re psi.im - lam.im psi.re, kept as the pair (lam.re psi.im, lam.im psi.re)
             signed_sums2([&](int j) { return __fmul2_rn(ls[j], swp(ps[j])); }, tot2, S2);
+            const float tot = tot2.x - tot2.y;
+            // all (up to ten) per-bit sums in one halving butterfly; lane l ends up with component l >> 1
+            float t16[16];
 #pragma unroll
-            for (int r = 0; r < kR; ++r) {
-              const int ai = D->acc_reg[r];
-              if (ai >= 0) { const float v = warp_sum(S2[r].x - S2[r].y); if (lane == 0) wacc[ai] += v; }
-            }
-            if (op.kind == MOP_DIAG) {
-              const float tot = tot2.x - tot2.y;
+            for (int r = 0; r < kR; ++r) t16[r] = S2[r].x - S2[r].y;
 #pragma unroll
-              for (int b = 0; b < 5; ++b) {
-                const int ai = D->acc_lane[b];
-                if (ai >= 0) { const float v = warp_sum(((lis >> b) & 1) ? -tot : tot); if (lane == 0) wacc[ai] += v; }
-              }
-              diag_mul<true, true>(ps, ls, S.big + op.idx * 1024, 32, lane);
-            } else {
-              diag_mul<true, true>(ps, ls, S.small + op.idx * 32, 1, 0);
+            for (int b = 0; b < 5; ++b) t16[kR + b] = ((lis >> b) & 1) ? -tot : tot;
+#pragma unroll
+            for (int k = 10; k < 16; ++k) t16[k] = 0.f;
+            const float r = warp_sum16(t16, lane);
+            if ((lane & 1) == 0) {
+              const int comp = lane >> 1;
+              const int ai = comp < kR ? D->acc_reg[comp] : (comp < 10 && op.pad0 == H_DIAG ? D->acc_lane[comp - kR] : -1);
+              if (ai >= 0) wacc[ai] += r;
             }
+            if (op.pad0 == H_DIAG) diag_mul<true, true>(ps, ls, S.big + op.idx * 1024, 32, lane);
+            else diag_mul<true, true>(ps, ls, S.small + op.idx * 32, 1, 0);
           } break;
-          case MOP_XCHG:
+          case H_XCHG:
             exchange(ps, S.xbuf, S.exchanges + op.idx, lane, true);
             exchange(ls, S.xbuf, S.exchanges + op.idx, lane, true);
             break;
           default: break;
         }
         op = next;
+        cfa = ncfa;
       }
       // ================= input gradients of this warp's samples =================
       __syncwarp();
@@ -705,7 +744,7 @@ constexpr size_t kSmemMax = 227 * 1024;
 struct Variant { int fwd_threads, bwd_threads; };
 Variant variant() {
   static Variant v = [] {
-    Variant r{512, 384};
+    Variant r{512, 256};
     if (const char* e = getenv("QNN_VM_VARIANT")) {   // tuning knob: "<fwd threads>,<bwd threads>"
       int a = 0, b = 0;
       if (sscanf(e, "%d,%d", &a, &b) == 2 && (a == 256 || a == 512) && (b == 256 || b == 384)) { r.fwd_threads = a; r.bwd_threads = b; }
@@ -730,6 +769,7 @@ void fill_args(const qnn_circuit* c, const Program& p, const Plan& pl, void* ws,
   a->big = reinterpret_cast<const float2*>(wsb + pl.ws_coef); a->n_big = p.n_big_tables;
   a->small = a->big + (size_t)p.n_big_tables * 1024; a->n_small = p.n_small_tables;
   a->n = p.n; a->tb = p.tb; a->n_inputs = c->n_inputs; a->n_acc = p.n_acc;
+  { const char* e = getenv("QNN_VM_SKIP"); a->skip_mask = e ? (unsigned)strtoul(e, nullptr, 0) : 0u; }
   for (int b = 0; b < 16; ++b) a->wire_of_bit[b] = 0;
   for (int w = 0; w < p.n; ++w) a->wire_of_bit[p.final_bit_of_wire[w]] = (int8_t)w;
   a->partial = reinterpret_cast<float*>(wsb + pl.ws_coef + pl.ws_diag);

@@ -41,7 +41,14 @@ enum MopKind : int32_t {
 };
 
 struct MicroOp {       // 32 bytes
-  int32_t kind, a, b, idx, acc, aux, pad0, pad1;
+  int32_t kind, a, b, idx, acc, aux;
+  int32_t pad0;        // handler id (enum Handler): kind and register bits folded into one dense jump index
+  int32_t pad1;        // coefficient row the kernel prefetches for this op (0 if none)
+};
+
+enum Handler : int32_t {
+  H_END = 0, H_ROT = 1, H_ROTX = 6, H_CU3L = 11, H_CU3P = 31, H_DIAG = 36, H_DIAGR = 37, H_XCHG = 38,
+  H_ROT5 = 39, H_ROTX5 = 40, H_CHAIN = 41,
 };
 
 struct DiagTerm {      // one factor of a diagonal: RZ(angle) on a physical bit, or CZ on two bits

@@ -399,6 +399,27 @@ struct Builder {
     P->ops.swap(out);
   }
 
+  // One dense handler id per (kind, register bits): the kernel dispatches with a single jump.
+  // pad1 = coefficient row to prefetch (0 when the op has none).
+  void assign_handlers() {
+    for (MicroOp& m : P->ops) {
+      m.pad1 = 0;
+      switch (m.kind) {
+        case MOP_ROT: m.pad0 = H_ROT + m.a; m.pad1 = m.idx; break;
+        case MOP_ROT_X: m.pad0 = H_ROTX + m.a; break;
+        case MOP_CU3_L: m.pad0 = H_CU3L + m.a * 4 + (m.b < m.a ? m.b : m.b - 1); m.pad1 = m.idx; break;
+        case MOP_CU3_P: m.pad0 = H_CU3P + m.a; m.pad1 = m.idx; break;
+        case MOP_DIAG: m.pad0 = H_DIAG; break;
+        case MOP_DIAG_REG: m.pad0 = H_DIAGR; break;
+        case MOP_XCHG: m.pad0 = H_XCHG; break;
+        case MOP_ROT5: m.pad0 = H_ROT5; break;
+        case MOP_ROTX5: m.pad0 = H_ROTX5; break;
+        case MOP_CU3_CHAIN: m.pad0 = H_CHAIN; m.pad1 = m.idx; break;
+        default: m.pad0 = H_END; break;
+      }
+    }
+  }
+
   bool all_clean() const {
     uint32_t seen = 0;
     for (int w = 0; w < n; ++w) {
@@ -479,6 +500,7 @@ struct Builder {
     }
     for (int w = 0; w < n; ++w) P->final_bit_of_wire[w] = bit_of(w);
     fuse_groups();
+    assign_handlers();
     MicroOp e{};
     e.kind = MOP_END; e.acc = -1;
     P->ops.push_back(e);
