@@ -247,7 +247,7 @@ def run_b200(args, wl):
 
     def step():
         wn = w + 0.01 * torch.randn_like(w) if qnat else w           # weight-space noise (Est:186-188)
-        y = qris_b200.qnn_forward_raw(circ, x, wn)
+        y, state = qris_b200.qnn_forward_raw(circ, x, wn, save_state=True)   # keeps psi_final for the adjoint pass
         if qnat:
             yq = y.detach().requires_grad_(True)
             out = head(yq)
@@ -255,7 +255,7 @@ def run_b200(args, wl):
             gy = yq.grad
         else:
             gy = gout
-        gx, _ = qris_b200.qnn_backward_raw(circ, x, wn, gy, need_gx=True, gw_out=gw_bucket)
+        gx, _ = qris_b200.qnn_backward_raw(circ, x, wn, gy, need_gx=True, gw_out=gw_bucket, state=state)
         if world > 1:
             dist.all_reduce(gw_bucket)
         return gx
@@ -283,9 +283,9 @@ def run_b200(args, wl):
         for _ in range(max(5, min(args.steps, 20))):
             flush.zero_()
             s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            s.record(); qris_b200.qnn_backward_raw(circ, x, w, gy_fixed, need_gx=True, gw_out=gw_bucket); e.record()
             s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            s2.record(); qris_b200.qnn_forward_raw(circ, x, w); e2.record()
+            s2.record(); _, st_k = qris_b200.qnn_forward_raw(circ, x, w, save_state=True); e2.record()
+            s.record(); qris_b200.qnn_backward_raw(circ, x, w, gy_fixed, need_gx=True, gw_out=gw_bucket, state=st_k); e.record()
             torch.cuda.synchronize()
             k_bwd.append(s.elapsed_time(e)); k_fwd.append(s2.elapsed_time(e2))
     t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
@@ -369,7 +369,7 @@ def run_b200(args, wl):
                     "d2h_bytes_per_step": 4},
             "gpu_launches": launches_per_step * args.steps + e2e_launches * args.steps,
             "roofline": {
-                "bound": "fp32", "kernel": "qnn_backward (adjoint VJP: recompute + uncompute + gradients)",
+                "bound": "fp32", "kernel": "qnn_backward_saved (adjoint VJP from the saved final state: uncompute + gradients)",
                 "achieved": achieved, "peak": FP32_PEAK_NOMINAL_TFLOPS, "unit": "TFLOP/s",
                 "frac": achieved / FP32_PEAK_NOMINAL_TFLOPS,
                 "peak_source": "nominal 148 SM x 128 lanes x 2 x 1.965 GHz (MEASURED_PEAKS.json has no FP32 entry)",

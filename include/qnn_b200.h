@@ -109,6 +109,20 @@ QNN_API int qnn_forward(const qnn_circuit* c, const float* x, const float* w, fl
 QNN_API int qnn_backward(const qnn_circuit* c, const float* x, const float* w, const float* gy, float* gx,
                  float* gw, int64_t B, void* workspace, size_t workspace_bytes, void* cuda_stream);
 
+/* Forward that also keeps the final statevector of every sample, and the backward that starts from it
+ * instead of re-running the forward program (the adjoint method needs psi_final; nothing per gate is
+ * ever stored).  This is the pair autograd uses: what the reference's backprop keeps alive between
+ * `self.qlayer(x)` (Est:191,199) and `loss.backward()` (Run:364) is ~60 intermediate states per sample,
+ * here it is one.  `state` is an opaque device buffer of qnn_state_bytes(c, B) bytes (2^n * 8 per
+ * sample, rounded up to whole warps); 0 means the circuit runs on the generic kernels, which recompute.
+ * x, w and B given to qnn_backward_saved must be those of the qnn_forward_save that wrote `state`. */
+QNN_API size_t qnn_state_bytes(const qnn_circuit* c, int64_t B);
+QNN_API int qnn_forward_save(const qnn_circuit* c, const float* x, const float* w, float* y, float* state,
+                             int64_t B, void* workspace, size_t workspace_bytes, void* cuda_stream);
+QNN_API int qnn_backward_saved(const qnn_circuit* c, const float* x, const float* w, const float* gy,
+                               const float* state, float* gx, float* gw, int64_t B, void* workspace,
+                               size_t workspace_bytes, void* cuda_stream);
+
 /* No counterpart in the reference.  Same result as qnn_backward, for callers that cannot supply a
  * workspace because they may not allocate device memory once running: real-time loops (a per-slot
  * channel-estimation service) where cudaMalloc's device-wide synchronisation and unbounded latency

@@ -31,5 +31,16 @@ ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
 ev[0].record(); y = qris_b200.qnn_forward_raw(circ, x, w); ev[1].record()
 gx, gw = qris_b200.qnn_backward_raw(circ, x, w, gy); ev[2].record()
 torch.cuda.synchronize()
+for _ in range(2):
+    _, state = qris_b200.qnn_forward_raw(circ, x, w, save_state=True)
+    qris_b200.qnn_backward_raw(circ, x, w, gy, state=state)
+del state
+torch.cuda.synchronize()
+ev2 = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+ev2[0].record(); y2, state = qris_b200.qnn_forward_raw(circ, x, w, save_state=True); ev2[1].record()
+gx2, gw2 = qris_b200.qnn_backward_raw(circ, x, w, gy, state=state); ev2[2].record()
+torch.cuda.synchronize()
+print(f"   with saved state: fwd {ev2[0].elapsed_time(ev2[1]):.3f} ms, bwd {ev2[1].elapsed_time(ev2[2]):.3f} ms, "
+      f"max|dgw| vs recompute {float((gw2 - gw).abs().max()):.2e}, max|dgx| {float((gx2 - gx).abs().max()):.2e}")
 print(f"{wl} B={B}: fwd {ev[0].elapsed_time(ev[1]):.3f} ms, bwd {ev[1].elapsed_time(ev[2]):.3f} ms, "
       f"plan {qris_b200._lib.lib().qnn_circuit_plan(circ.handle(0), B).decode()}")

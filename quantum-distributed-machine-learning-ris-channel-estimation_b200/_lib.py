@@ -50,6 +50,9 @@ SIGNATURES = {
     "qnn_backward_workspace_bytes": (_sz, [_vp, _i64]),
     "qnn_forward": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _sz, _vp]),
     "qnn_backward": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _vp]),
+    "qnn_state_bytes": (_sz, [_vp, _i64]),
+    "qnn_forward_save": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _vp]),
+    "qnn_backward_saved": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _vp]),
     "qnn_static_scratch_bytes": (_sz, []),
     "qnn_backward_static": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp]),
     "qnat_workspace_bytes": (_sz, [_i64, _i32]),

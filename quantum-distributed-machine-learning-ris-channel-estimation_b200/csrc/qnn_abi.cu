@@ -221,38 +221,70 @@ static int check_common(const char* fn, const qnn_circuit* c, const float* x, co
   return QNN_OK;
 }
 
-extern "C" int qnn_forward(const qnn_circuit* c, const float* x, const float* w, float* y, int64_t B,
-                           void* workspace, size_t workspace_bytes, void* cuda_stream) {
-  int rc = check_common("qnn_forward", c, x, w, B);
+extern "C" size_t qnn_state_bytes(const qnn_circuit* c, int64_t B) {
+  if (!c || B <= 0) return 0;
+  vm::Plan vp;
+  return vm_plan(c, B, &vp) ? vm::state_bytes(*c->vm, B) : 0;
+}
+
+static int forward_impl(const char* fn, const qnn_circuit* c, const float* x, const float* w, float* y, float* state,
+                        int64_t B, void* workspace, size_t workspace_bytes, void* cuda_stream) {
+  int rc = check_common(fn, c, x, w, B);
   if (rc) return rc;
-  if (!y) { qnn_set_error("qnn_forward: y is NULL"); return QNN_ERR_INVALID; }
+  if (!y) { qnn_set_error("%s: y is NULL", fn); return QNN_ERR_INVALID; }
   const size_t need = qnn_forward_workspace_bytes(c, B);
   if (need > 0 && (!workspace || workspace_bytes < need)) {
-    qnn_set_error("qnn_forward: workspace of %zu bytes needed, %zu given", need, workspace ? workspace_bytes : (size_t)0);
+    qnn_set_error("%s: workspace of %zu bytes needed, %zu given", fn, need, workspace ? workspace_bytes : (size_t)0);
     return QNN_ERR_WORKSPACE;
   }
   vm::Plan vp;
-  if (vm_plan(c, B, &vp)) return vm::forward(c, *c->vm, vp, x, w, y, B, workspace, static_cast<cudaStream_t>(cuda_stream));
+  if (vm_plan(c, B, &vp)) return vm::forward(c, *c->vm, vp, x, w, y, B, workspace, state, static_cast<cudaStream_t>(cuda_stream));
+  if (state) { qnn_set_error("%s: this circuit runs on the generic kernels, which keep no state (qnn_state_bytes() is 0)", fn); return QNN_ERR_UNSUPPORTED; }
   GenericPlan p;
   generic_plan(c, B, &p);
   return generic_forward(c, p, x, w, y, B, workspace, static_cast<cudaStream_t>(cuda_stream));
 }
 
-extern "C" int qnn_backward(const qnn_circuit* c, const float* x, const float* w, const float* gy,
-                            float* gx, float* gw, int64_t B, void* workspace, size_t workspace_bytes,
-                            void* cuda_stream) {
-  int rc = check_common("qnn_backward", c, x, w, B);
+static int backward_impl(const char* fn, const qnn_circuit* c, const float* x, const float* w, const float* gy,
+                         const float* state, float* gx, float* gw, int64_t B, void* workspace, size_t workspace_bytes,
+                         void* cuda_stream) {
+  int rc = check_common(fn, c, x, w, B);
   if (rc) return rc;
-  if (!gy) { qnn_set_error("qnn_backward: gy is NULL"); return QNN_ERR_INVALID; }
-  if (!gw && c->n_weights > 0) { qnn_set_error("qnn_backward: gw is NULL"); return QNN_ERR_INVALID; }
+  if (!gy) { qnn_set_error("%s: gy is NULL", fn); return QNN_ERR_INVALID; }
+  if (!gw && c->n_weights > 0) { qnn_set_error("%s: gw is NULL", fn); return QNN_ERR_INVALID; }
   const size_t need = qnn_backward_workspace_bytes(c, B);
   if (!workspace || workspace_bytes < need) {
-    qnn_set_error("qnn_backward: workspace of %zu bytes needed, %zu given", need, workspace ? workspace_bytes : (size_t)0);
+    qnn_set_error("%s: workspace of %zu bytes needed, %zu given", fn, need, workspace ? workspace_bytes : (size_t)0);
     return QNN_ERR_WORKSPACE;
   }
   vm::Plan vp;
-  if (vm_plan(c, B, &vp)) return vm::backward(c, *c->vm, vp, x, w, gy, gx, gw, B, workspace, static_cast<cudaStream_t>(cuda_stream));
+  if (vm_plan(c, B, &vp)) return vm::backward(c, *c->vm, vp, x, w, gy, gx, gw, B, workspace, state, static_cast<cudaStream_t>(cuda_stream));
+  if (state) { qnn_set_error("%s: this circuit runs on the generic kernels, which keep no state (qnn_state_bytes() is 0)", fn); return QNN_ERR_UNSUPPORTED; }
   GenericPlan p;
   generic_plan(c, B, &p);
   return generic_backward(c, p, x, w, gy, gx, gw, B, workspace, static_cast<cudaStream_t>(cuda_stream));
+}
+
+extern "C" int qnn_forward(const qnn_circuit* c, const float* x, const float* w, float* y, int64_t B,
+                           void* workspace, size_t workspace_bytes, void* cuda_stream) {
+  return forward_impl("qnn_forward", c, x, w, y, nullptr, B, workspace, workspace_bytes, cuda_stream);
+}
+
+extern "C" int qnn_forward_save(const qnn_circuit* c, const float* x, const float* w, float* y, float* state,
+                                int64_t B, void* workspace, size_t workspace_bytes, void* cuda_stream) {
+  if (!state) { qnn_set_error("qnn_forward_save: state is NULL"); return QNN_ERR_INVALID; }
+  return forward_impl("qnn_forward_save", c, x, w, y, state, B, workspace, workspace_bytes, cuda_stream);
+}
+
+extern "C" int qnn_backward(const qnn_circuit* c, const float* x, const float* w, const float* gy,
+                            float* gx, float* gw, int64_t B, void* workspace, size_t workspace_bytes,
+                            void* cuda_stream) {
+  return backward_impl("qnn_backward", c, x, w, gy, nullptr, gx, gw, B, workspace, workspace_bytes, cuda_stream);
+}
+
+extern "C" int qnn_backward_saved(const qnn_circuit* c, const float* x, const float* w, const float* gy,
+                                  const float* state, float* gx, float* gw, int64_t B, void* workspace,
+                                  size_t workspace_bytes, void* cuda_stream) {
+  if (!state) { qnn_set_error("qnn_backward_saved: state is NULL"); return QNN_ERR_INVALID; }
+  return backward_impl("qnn_backward_saved", c, x, w, gy, state, gx, gw, B, workspace, workspace_bytes, cuda_stream);
 }

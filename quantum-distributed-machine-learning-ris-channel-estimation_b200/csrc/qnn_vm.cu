@@ -38,6 +38,7 @@ struct VmArgs {
   int8_t wire_of_bit[16];                   // final (measurement) layout
   const float* x; float* y;                 // forward
   const float* gy; float* gx; float* partial;  // backward; partial [grid][n_acc]
+  float4* state;                            // optional: final psi of every warp-batch (forward writes, backward reads)
   long long B;
 };
 
@@ -365,7 +366,7 @@ size_t smem_bytes(const Program& p, int n_inputs, int warps, bool bwd) {
   return b + 256;  // per-array 16-byte alignment slack
 }
 
-template <bool BWD, int THREADS, int MINB>
+template <bool BWD, int THREADS, int MINB, bool STATE>
 __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -430,6 +431,16 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
     __syncwarp();
     const float2* const xc = xcoef + siw * a.n_inputs;
 
+    // Saved final state: [batch][j / 2][lane] float4 = amplitudes (2 * (j/2), 2 * (j/2) + 1) of that lane;
+    // a warp reads or writes 512 contiguous bytes per instruction.
+    float4* const st_rows = STATE ? a.state + (size_t)wb * (NA / 2) * 32 + lane : nullptr;
+    if constexpr (BWD && STATE) {
+#pragma unroll
+      for (int q = 0; q < NA / 2; ++q) {
+        const float4 v = __ldcs(st_rows + q * 32);
+        ps[2 * q] = make_float2(v.x, v.y); ps[2 * q + 1] = make_float2(v.z, v.w);
+      }
+    } else {
 #pragma unroll
     for (int j = 0; j < NA; ++j) ps[j] = make_float2(0.f, 0.f);
     ps[0].x = lis == 0 ? 1.f : 0.f;
@@ -489,6 +500,13 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
         op = next;
         cfa = ncfa;
       }
+    }
+    }  // forward program (skipped when the backward pass starts from a saved state)
+
+    if constexpr (!BWD && STATE) {
+#pragma unroll
+      for (int q = 0; q < NA / 2; ++q)
+        __stcs(st_rows + q * 32, make_float4(ps[2 * q].x, ps[2 * q].y, ps[2 * q + 1].x, ps[2 * q + 1].y));
     }
 
     if constexpr (!BWD) {
@@ -788,6 +806,11 @@ int launch_prep(const Program& p, const float* w, const VmArgs& a, cudaStream_t 
 
 }  // namespace
 
+size_t state_bytes(const Program& p, int64_t B) {
+  const int64_t spw = 32 >> p.tb;
+  return (size_t)((B + spw - 1) / spw) * kWarpAmps * sizeof(float2);
+}
+
 bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
   if (!p.ok) return false;
   const Variant v = variant();
@@ -848,10 +871,10 @@ void release(Program* p) {
 }
 
 int forward(const qnn_circuit* c, const Program& p, const Plan& pl, const float* x, const float* w, float* y,
-            int64_t B, void* ws, cudaStream_t st) {
+            int64_t B, void* ws, float* state, cudaStream_t st) {
   VmArgs a{};
   fill_args(c, p, pl, ws, &a);
-  a.x = x; a.y = y; a.B = B;
+  a.x = x; a.y = y; a.B = B; a.state = reinterpret_cast<float4*>(state);
   int rc = launch_prep(p, w, a, st);
   if (rc) return rc;
   const Variant v = variant();
@@ -866,15 +889,16 @@ int forward(const qnn_circuit* c, const Program& p, const Plan& pl, const float*
     QNN_CUDA_CHECK(cudaGetLastError());
     return QNN_OK;
   };
-  if (v.fwd_threads == 512) return go(k_vm<false, 512, 1>, 1);
-  return go(k_vm<false, 256, 2>, 2);
+  if (a.state) return v.fwd_threads == 512 ? go(k_vm<false, 512, 1, true>, 1) : go(k_vm<false, 256, 2, true>, 2);
+  if (v.fwd_threads == 512) return go(k_vm<false, 512, 1, false>, 1);
+  return go(k_vm<false, 256, 2, false>, 2);
 }
 
 int backward(const qnn_circuit* c, const Program& p, const Plan& pl, const float* x, const float* w,
-             const float* gy, float* gx, float* gw, int64_t B, void* ws, cudaStream_t st) {
+             const float* gy, float* gx, float* gw, int64_t B, void* ws, const float* state, cudaStream_t st) {
   VmArgs a{};
   fill_args(c, p, pl, ws, &a);
-  a.x = x; a.gy = gy; a.gx = gx; a.B = B;
+  a.x = x; a.gy = gy; a.gx = gx; a.B = B; a.state = reinterpret_cast<float4*>(const_cast<float*>(state));
   int rc = launch_prep(p, w, a, st);
   if (rc) return rc;
   const Variant v = variant();
@@ -885,8 +909,9 @@ int backward(const qnn_circuit* c, const Program& p, const Plan& pl, const float
     QNN_CUDA_CHECK(cudaGetLastError());
     return QNN_OK;
   };
-  if (v.bwd_threads == 384) rc = go(k_vm<true, 384, 1>);
-  else rc = go(k_vm<true, 256, 1>);
+  if (a.state) rc = go(k_vm<true, 256, 1, true>);
+  else if (v.bwd_threads == 384) rc = go(k_vm<true, 384, 1, false>);
+  else rc = go(k_vm<true, 256, 1, false>);
   if (rc) return rc;
   if (c->n_weights > 0) {
     k_vm_finalize<<<c->n_weights, 128, 0, st>>>(a.partial, pl.grid, p.n_acc, p.d_slots, p.d_slot_ptr, p.d_slot_idx, gw);

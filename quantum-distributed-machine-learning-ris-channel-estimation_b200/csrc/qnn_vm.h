@@ -111,9 +111,12 @@ struct Plan {
 bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out);
 int upload(Program* p, int n_weights);
 void release(Program* p);
+size_t state_bytes(const Program& p, int64_t B);
+// state: optional device buffer of state_bytes(): forward stores the final statevector of every sample
+// there, backward then starts from it instead of re-running the forward program.
 int forward(const qnn_circuit* c, const Program& p, const Plan& pl, const float* x, const float* w, float* y,
-            int64_t B, void* ws, cudaStream_t st);
+            int64_t B, void* ws, float* state, cudaStream_t st);
 int backward(const qnn_circuit* c, const Program& p, const Plan& pl, const float* x, const float* w,
-             const float* gy, float* gx, float* gw, int64_t B, void* ws, cudaStream_t st);
+             const float* gy, float* gx, float* gw, int64_t B, void* ws, const float* state, cudaStream_t st);
 
 }  // namespace vm

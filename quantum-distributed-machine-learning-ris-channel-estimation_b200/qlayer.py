@@ -32,30 +32,41 @@ def _workspace(nbytes: int, device) -> Optional[torch.Tensor]:
     return torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=device)
 
 
-def qnn_forward_raw(circuit: Circuit, x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
-    """One ``qnn_forward`` call on the current stream.  x (B, n_inputs), w (n_weights,) float32 CUDA."""
+def qnn_forward_raw(circuit: Circuit, x: torch.Tensor, w: torch.Tensor, save_state: bool = False):
+    """One ``qnn_forward`` call on the current stream.  x (B, n_inputs), w (n_weights,) float32 CUDA.
+
+    ``save_state=True`` returns ``(y, state)`` where ``state`` is the opaque final-statevector buffer that
+    ``qnn_backward_raw(..., state=state)`` starts from (``None`` if the circuit's kernels keep none)."""
     lib = _lib.lib()
     B = x.shape[0]
     y = torch.empty((B, circuit.n_qubits), dtype=torch.float32, device=x.device)
     if B == 0:
-        return y
+        return (y, None) if save_state else y
     dev = x.device.index if x.device.index is not None else torch.cuda.current_device()
     h = circuit.handle(dev)
+    state = None
     with torch.cuda.device(dev):
         ws = _workspace(lib.qnn_forward_workspace_bytes(h, B), x.device)
         st = torch.cuda.current_stream(dev).cuda_stream
-        rc = lib.qnn_forward(h, _ptr(x), _ptr(w), _ptr(y), B, _ptr(ws), ws.numel(), st)
+        nbytes = lib.qnn_state_bytes(h, B) if save_state else 0
+        if nbytes > 0:
+            state = torch.empty(nbytes // 4, dtype=torch.float32, device=x.device)
+            rc = lib.qnn_forward_save(h, _ptr(x), _ptr(w), _ptr(y), _ptr(state), B, _ptr(ws), ws.numel(), st)
+        else:
+            rc = lib.qnn_forward(h, _ptr(x), _ptr(w), _ptr(y), B, _ptr(ws), ws.numel(), st)
     _lib.check(rc, "qnn_forward")
-    return y
+    return (y, state) if save_state else y
 
 
 def qnn_backward_raw(circuit: Circuit, x: torch.Tensor, w: torch.Tensor, gy: torch.Tensor,
-                     need_gx: bool = True, gw_out: Optional[torch.Tensor] = None
+                     need_gx: bool = True, gw_out: Optional[torch.Tensor] = None,
+                     state: Optional[torch.Tensor] = None
                      ) -> Tuple[Optional[torch.Tensor], torch.Tensor]:
     """One ``qnn_backward`` call on the current stream -> (gx or None, gw).
 
     ``gw_out``: optional preallocated float32 view (e.g. a slice of a flat gradient bucket) that the
-    kernel overwrites directly."""
+    kernel overwrites directly.  ``state``: the buffer ``qnn_forward_raw(..., save_state=True)`` returned
+    for the same (x, w); without it the backward kernel re-runs the forward program first."""
     lib = _lib.lib()
     B = x.shape[0]
     gw = gw_out if gw_out is not None else torch.empty((circuit.n_weights,), dtype=torch.float32, device=x.device)
@@ -68,9 +79,17 @@ def qnn_backward_raw(circuit: Circuit, x: torch.Tensor, w: torch.Tensor, gy: tor
     with torch.cuda.device(dev):
         ws = _workspace(lib.qnn_backward_workspace_bytes(h, B), x.device)
         st = torch.cuda.current_stream(dev).cuda_stream
-        rc = lib.qnn_backward(h, _ptr(x), _ptr(w), _ptr(gy), _ptr(gx), _ptr(gw), B, _ptr(ws), ws.numel(), st)
+        if state is not None:
+            rc = lib.qnn_backward_saved(h, _ptr(x), _ptr(w), _ptr(gy), _ptr(state), _ptr(gx), _ptr(gw), B,
+                                        _ptr(ws), ws.numel(), st)
+        else:
+            rc = lib.qnn_backward(h, _ptr(x), _ptr(w), _ptr(gy), _ptr(gx), _ptr(gw), B, _ptr(ws), ws.numel(), st)
     _lib.check(rc, "qnn_backward")
     return gx, gw
+
+
+# Keep the final state for backward only while it stays modest (2^n * 8 bytes per sample).
+STATE_SAVE_LIMIT_BYTES = 4 << 30
 
 
 class _QNNFunction(torch.autograd.Function):
@@ -83,8 +102,11 @@ class _QNNFunction(torch.autograd.Function):
         # runs the forward and restores them BEFORE backward; its autograd graph holds values computed
         # from the noisy weights.  A recomputing backward must therefore own a copy of what it used.
         wc = w.detach().to(torch.float32).contiguous().clone()
-        y = qnn_forward_raw(circuit, xc, wc)
+        need_grad = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
+        save = need_grad and xc.shape[0] * (8 << circuit.n_qubits) <= STATE_SAVE_LIMIT_BYTES
+        y, state = qnn_forward_raw(circuit, xc, wc, save_state=True) if save else (qnn_forward_raw(circuit, xc, wc), None)
         ctx.circuit = circuit
+        ctx.state = state
         ctx.save_for_backward(xc, wc)
         ctx.x_dtype, ctx.w_dtype = x.dtype, w.dtype
         return y.to(x.dtype) if x.dtype != torch.float32 else y
@@ -94,7 +116,8 @@ class _QNNFunction(torch.autograd.Function):
     def backward(ctx, gy):
         xc, wc = ctx.saved_tensors
         gyc = gy.detach().to(torch.float32).contiguous()
-        gx, gw = qnn_backward_raw(ctx.circuit, xc, wc, gyc, need_gx=ctx.needs_input_grad[0])
+        gx, gw = qnn_backward_raw(ctx.circuit, xc, wc, gyc, need_gx=ctx.needs_input_grad[0], state=ctx.state)
+        ctx.state = None
         if gx is not None and ctx.x_dtype != torch.float32:
             gx = gx.to(ctx.x_dtype)
         if not ctx.needs_input_grad[1]:

@@ -198,3 +198,24 @@ def test_vm_irregular_circuit():
     circ = qris_b200.Circuit(n, ops, n_inputs=n, n_weights=9)
     assert _plan(circ, 10) == "vm-register"
     check_against_oracle(circ, 45, seed=2)
+
+
+@pytest.mark.parametrize("make,B", [(lambda: qris_b200.u3cu3_circuit(10, 2), 100), (lambda: qris_b200.reference_circuit(6, 3), 300),
+                                     (lambda: qris_b200.reference_circuit(7, 2), 33), (lambda: qris_b200.reference_circuit(4, 2), 20)])
+def test_backward_from_saved_state_matches_recompute(make, B):
+    """qnn_forward_save / qnn_backward_saved (the autograd pair) against qnn_forward / qnn_backward."""
+    circ = make()
+    x, w, gy = (t.cuda() for t in seeded_inputs(circ, B, seed=11))
+    y0 = qris_b200.qnn_forward_raw(circ, x, w)
+    y1, state = qris_b200.qnn_forward_raw(circ, x, w, save_state=True)
+    assert torch.equal(y0, y1)
+    lib = qris_b200._lib.lib()
+    nbytes = lib.qnn_state_bytes(circ.handle(0), B)
+    if circ.n_qubits < 5:
+        assert state is None and nbytes == 0          # generic kernels recompute
+    else:
+        assert state is not None and state.numel() * 4 == nbytes and nbytes >= B * (8 << circ.n_qubits)
+    gx0, gw0 = qris_b200.qnn_backward_raw(circ, x, w, gy)
+    gx1, gw1 = qris_b200.qnn_backward_raw(circ, x, w, gy, state=state)
+    assert_close(gx1.cpu().numpy(), gx0.cpu().numpy(), scale=float(gx0.abs().max()), what="gx")
+    assert_close(gw1.cpu().numpy(), gw0.cpu().numpy(), scale=float(gw0.abs().max()), what="gw")
