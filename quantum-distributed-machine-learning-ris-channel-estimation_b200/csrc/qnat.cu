@@ -66,12 +66,15 @@ __global__ void __launch_bounds__(kThreads) k_col_sums(const float* __restrict__
   }
 }
 
+// One warp per column; lanes stride over the CTA partials, then a shuffle tree: fixed order.
 __global__ void k_sum_partials(const double* __restrict__ partial, int n_ctas, int n2, double* __restrict__ sums) {
-  const int j = threadIdx.x;
+  const int j = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (j >= n2) return;
   double t = 0.0;
-  for (int c = 0; c < n_ctas; ++c) t += partial[(size_t)c * n2 + j];
-  sums[j] = t;
+  for (int c = lane; c < n_ctas; c += 32) t += partial[(size_t)c * n2 + j];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  if (lane == 0) sums[j] = t;
 }
 
 __global__ void __launch_bounds__(kThreads) k_apply(const float* __restrict__ y, const float* __restrict__ noise,
@@ -154,7 +157,7 @@ extern "C" int qnat_batch_sums(const float* y, double* sums, int64_t B, int32_t 
   qnat_params p{};
   k_col_sums<0><<<g, kThreads, 0, st>>>(y, nullptr, nullptr, nullptr, B, n, p, static_cast<double*>(workspace));
   QNN_CUDA_CHECK(cudaGetLastError());
-  k_sum_partials<<<1, 32, 0, st>>>(static_cast<double*>(workspace), g, 2 * n, sums);
+  k_sum_partials<<<1, 32 * 2 * n, 0, st>>>(static_cast<double*>(workspace), g, 2 * n, sums);
   QNN_CUDA_CHECK(cudaGetLastError());
   return QNN_OK;
 }
@@ -182,7 +185,7 @@ extern "C" int qnat_backward_sums(const float* gout, const float* y, const float
   const int g = n_ctas_for(B, n);
   k_col_sums<1><<<g, kThreads, 0, st>>>(y, gout, yn, stats, B, n, *p, static_cast<double*>(workspace));
   QNN_CUDA_CHECK(cudaGetLastError());
-  k_sum_partials<<<1, 32, 0, st>>>(static_cast<double*>(workspace), g, 2 * n, bsums);
+  k_sum_partials<<<1, 32 * 2 * n, 0, st>>>(static_cast<double*>(workspace), g, 2 * n, bsums);
   QNN_CUDA_CHECK(cudaGetLastError());
   return QNN_OK;
 }
