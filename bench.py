@@ -55,8 +55,10 @@ def algorithmic_flops(ops, n):
     return fwd, bwd
 
 
-def hbm_bytes_per_sample(n):
-    return 20 * n   # fwd: read x, write y; bwd: read x, read gy, write gx (4 bytes each, n columns)
+def hbm_bytes_per_sample(n, saved_state=True):
+    """fwd: read x, write y; bwd: read x, gy, write gx (4 bytes each, n columns); plus, when the adjoint
+    pass starts from the saved final state, one write and one read of 2^n complex64 amplitudes."""
+    return 20 * n + (2 * 8 * (1 << n) if saved_state else 0)
 
 
 # ---- clocks ---------------------------------------------------------------------------------------
