@@ -166,6 +166,15 @@ QNN_API int qnat_backward_apply(const float* gout, const float* y, const float* 
                         const double* bsums, int64_t B_total, float* gy, int64_t B, int32_t n,
                         const qnat_params* p, void* cuda_stream);
 
+/* Fused optimiser tail over flat buffers: the reference's gradient pruning
+ * (zero g where |g| <= threshold, Est:205-228; pass a negative threshold to skip it) followed by one
+ * torch.optim.AdamW step (Run:320,369; amsgrad off), as one elementwise kernel.  `step` is the 1-based
+ * step count.  pruned_count (device, may be NULL) is incremented by the number of zeroed entries; grads
+ * are overwritten with their pruned values. */
+QNN_API int qnn_pruned_adamw_step(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
+                                  float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
+                                  float prune_threshold, unsigned long long* pruned_count, void* cuda_stream);
+
 /* Measured FP32 FMA throughput of the current device in TFLOP/s (register-resident FMA chains,
  * timed with CUDA events; synchronises).  Used only by bench.py for the roofline denominator. */
 QNN_API int qnn_fp32_peak_probe(int32_t iters, double* tflops, double* sm_clock_mhz_unused);

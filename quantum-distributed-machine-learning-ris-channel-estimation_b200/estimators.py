@@ -39,11 +39,11 @@ class DCE_P128(nn.Module):
 class SC_P128(nn.Module):
     """Classical scenario classifier (Est:79-101)."""
 
-    def __init__(self):
+    def __init__(self, pilot_hw=(16, 8)):
         super().__init__()
         self.conv1 = nn.Conv2d(2, 32, 3, padding=1, bias=False)
         self.conv2 = nn.Conv2d(32, 32, 3, padding=1, bias=False)
-        self.FC = nn.Linear(32 * 4 * 2, 3)
+        self.FC = nn.Linear(32 * (pilot_hw[0] // 4) * (pilot_hw[1] // 4), 3)
 
     def forward(self, x):
         x = F.max_pool2d(F.relu(self.conv1(x)), 2, 2)
@@ -54,13 +54,18 @@ class SC_P128(nn.Module):
 class QSC_P128(nn.Module):
     """Quantum scenario classifier (Est:107-228): CNN -> tanh angles -> QNN -> linear -> log-softmax.
 
+    ``pilot_hw`` (default 16 x 8 = the reference's P = 128, Run:345) sizes the flatten layer as
+    ``32 * (h/4) * (w/4)`` for the pilot-length sweep of BASELINE config 5; everything else is the
+    reference's.
+
     Differences from the reference are confined to what runs the circuit: ``self.qlayer`` is a
     ``TorchLayer`` over the CUDA kernels.  Construction consumes torch's RNG in the reference's order
     (quantum weights, then preprocess, then classifier: Est:149,152,165), so a given
     ``torch.manual_seed`` yields the same initial model.
     """
 
-    def __init__(self, n_qubits=6, n_layers=3, n_classes=3, use_quantumnat=True, use_gradient_pruning=True):
+    def __init__(self, n_qubits=6, n_layers=3, n_classes=3, use_quantumnat=True, use_gradient_pruning=True,
+                 pilot_hw=(16, 8)):
         super().__init__()
         self.use_quantum = True
         self.num_qubits = n_qubits
@@ -89,7 +94,7 @@ class QSC_P128(nn.Module):
         self.preprocess = nn.Sequential(                         # Est:152-162
             nn.Conv2d(2, 16, 3, stride=1, padding=1), nn.ReLU(), nn.MaxPool2d(2),
             nn.Conv2d(16, 32, 3, stride=1, padding=1), nn.ReLU(), nn.MaxPool2d(2),
-            nn.Flatten(), nn.Linear(32 * 4 * 2, n_qubits), nn.Tanh())
+            nn.Flatten(), nn.Linear(32 * (pilot_hw[0] // 4) * (pilot_hw[1] // 4), n_qubits), nn.Tanh())
         self.classifier = nn.Linear(n_qubits, n_classes)         # Est:165
 
     def forward(self, x):
@@ -135,7 +140,7 @@ class QSC_P128(nn.Module):
 class Conv_P128(nn.Module):
     """HDCE feature extractor (Est:237-268): (B,2,16,8) -> (B,4096)."""
 
-    def __init__(self):
+    def __init__(self, pilot_hw=(16, 8)):
         super().__init__()
         self.features, self.kernel_size, self.padding = 32, 3, 1
         self.cnn = _conv_bn_relu_stack(self.features)
@@ -147,9 +152,9 @@ class Conv_P128(nn.Module):
 class FC_P128(nn.Module):
     """HDCE feature mapper (Est:272-279): (B,4096) -> (B,2048)."""
 
-    def __init__(self):
+    def __init__(self, pilot_hw=(16, 8)):
         super().__init__()
-        self.FC = nn.Linear(32 * 16 * 8, 64 * 16 * 2)
+        self.FC = nn.Linear(32 * pilot_hw[0] * pilot_hw[1], 64 * 16 * 2)
 
     def forward(self, x):
         return self.FC(x)

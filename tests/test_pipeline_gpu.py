@@ -1,0 +1,134 @@
+"""GPU: the rows either side of the hot path: fused optimiser tail (N1), training loop
+on device-resident synthetic data (N4), routed NMSE-vs-SNR evaluation (N3), pilot-length variants."""
+import copy
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+import qris_b200
+from helpers import assert_close, oracle_ops
+from oracle import qnn_oracle as O
+from qris_b200 import data as D
+from qris_b200 import estimators as E
+from qris_b200 import evaluate, optim, runner
+
+pytestmark = pytest.mark.gpu
+
+
+class OracleQLayer(torch.nn.Module):      # checker only: the circuit evaluated by the CPU oracle
+    def __init__(self, circuit, weights):
+        super().__init__()
+        self.circuit, self.weights = circuit, torch.nn.Parameter(weights.detach().double().cpu().clone())
+
+    def forward(self, x):
+        return O.simulate(oracle_ops(self.circuit), self.circuit.n_qubits, x.double(), self.weights.reshape(-1))
+
+
+def oracle_twin(model):
+    twin = copy.deepcopy(model).cpu().double()
+    twin.qlayer = OracleQLayer(model.qlayer.circuit, model.qlayer.weights)
+    return twin
+
+
+@pytest.mark.parametrize("threshold", [None, 0.1])
+def test_fused_pruned_adamw_matches_torch(threshold):
+    """Est:205-228 pruning + torch.optim.AdamW (Run:320) against the one-kernel version, several steps."""
+    torch.manual_seed(0)
+    ref = torch.nn.Sequential(torch.nn.Linear(40, 30), torch.nn.Tanh(), torch.nn.Linear(30, 7)).cuda()
+    fast = copy.deepcopy(ref)
+    opt_ref = torch.optim.AdamW(ref.parameters(), lr=1e-3, weight_decay=0.01)
+    opt_fast = optim.FlatPrunedAdamW(fast.parameters(), lr=1e-3, weight_decay=0.01, prune_threshold=threshold)
+    n_pruned_ref = 0
+    for step in range(6):
+        x = torch.randn(64, 40, device="cuda"); y = torch.randint(0, 7, (64,), device="cuda")
+        opt_ref.zero_grad(); opt_fast.zero_grad()
+        (20 * F.cross_entropy(ref(x), y)).backward()
+        (20 * F.cross_entropy(fast(x), y)).backward()
+        if threshold is not None:                      # the reference's pruning, verbatim semantics
+            for p in ref.parameters():
+                mask = p.grad.abs() > threshold
+                n_pruned_ref += int((~mask).sum())
+                p.grad = p.grad * mask.float()
+        opt_ref.step(); opt_fast.step()
+    for a, b in zip(ref.parameters(), fast.parameters()):
+        assert_close(b.detach().cpu().numpy(), a.detach().cpu().numpy(), rel=2e-6, what="parameters after 6 steps")
+    if threshold is not None:
+        total = 6 * sum(p.numel() for p in ref.parameters())
+        assert abs(opt_fast.pruned_fraction() - n_pruned_ref / total) < 2e-3 and n_pruned_ref > 0
+    assert "0.weight" in fast.state_dict()             # Parameter objects (and checkpoint keys) untouched
+
+
+def test_qsc_training_step_matches_oracle_twin_with_torch_adamw():
+    """One full Run:338-369 step through runner.qsc_step (kernels + fused optimiser) vs the oracle twin."""
+    r = runner.Y2HRunner(data_len=200, batch_size_DML=16, device="cuda", verbose=False)
+    torch.manual_seed(0)
+    model = E.QSC_P128(use_quantumnat=False, use_gradient_pruning=False).cuda().train()
+    twin = oracle_twin(model).train()
+    opt = optim.FlatPrunedAdamW(model.parameters(), lr=1e-3, weight_decay=0.01)
+    opt_t = torch.optim.AdamW(twin.parameters(), lr=1e-3, weight_decay=0.01)
+    train_loader, _ = r.get_dataloader_DML()
+    sutd = next(iter(train_loader))
+    loss = r.qsc_step(model, opt, sutd)
+    opt_t.zero_grad()
+    loss_t = 0
+    for sid in range(3):
+        for uid in range(3):
+            yp, _, _, ind = sutd[sid][uid]
+            loss_t = loss_t + F.nll_loss(twin(D.pilot_image(yp, 128).cpu().double()), ind.cpu()) / 9
+    loss_t.backward(); opt_t.step()
+    assert abs(loss.item() - loss_t.item()) < 1e-5
+    for (k, p), (_, q) in zip(model.named_parameters(), twin.named_parameters()):
+        a, b = p.detach().cpu().numpy().copy(), q.detach().numpy().copy()
+        if k == "qlayer.weights":
+            # the last layer's RZ angles have an identically zero gradient; Adam divides
+            # rounding noise by itself there, so those six entries are not comparable across precisions
+            a[-1, :, 1] = b[-1, :, 1] = 0
+        assert_close(a, b, rel=5e-6, what=k)
+
+
+def test_short_training_run_learns_and_saves(tmp_path):
+    r = runner.Y2HRunner(data_len=1500, batch_size_DML=64, n_epochs=3, lr=5e-3, device="cuda", verbose=False,
+                         workdir=str(tmp_path))
+    hist = r.train_QSC_P128()
+    assert all(np.isfinite(hist["train_loss"])) and hist["train_loss"][-1] < hist["train_loss"][0]
+    assert 0.9 < hist["train_loss"][0] < 1.2             # starts near ln 3, as the reference's loss curve does
+    assert hist["val_acc"][-1] > 0.6                     # three separable scenarios: well above chance
+    saved = sorted(p.name for p in (tmp_path / "Pn_128" / "HDCE").iterdir())
+    assert "QSC_OPT_64_10dB_best_DML.pth" in saved and "QSC_OPT_64_10dB_epoch2_DML.pth" in saved
+    sd = torch.load(tmp_path / "Pn_128" / "HDCE" / "QSC_OPT_64_10dB_best_DML.pth")
+    E.QSC_P128().load_state_dict(sd)                     # reference-compatible keys
+
+
+def test_routed_nmse_parity_kernel_vs_oracle():
+    """BASELINE config 5's criterion at small scale: estimator NMSE with the kernel-backed quantum
+    classifier within 0.05 dB of the same pipeline driven by the oracle, identical argmax."""
+    r = runner.Y2HRunner(data_len=1000, batch_size_DML=50, n_epochs=3, lr=5e-3, device="cuda", verbose=False)
+    r.train_QSC_P128(save=False)
+    r.train_Conv_Linear_of_HDCE(n_epochs=1, max_iters_per_epoch=6)
+    gen = D.SyntheticRIS(128, seed=0, device="cuda")
+    twin = oracle_twin(r.model_QSC).eval()
+
+    class OracleClassifier(torch.nn.Module):             # evaluates on the CPU oracle, answers on the GPU
+        def forward(self, img):
+            with torch.no_grad():
+                return twin(img.cpu().double()).float().cuda()
+    res = evaluate.snr_sweep(gen, {"quantum": r.model_QSC, "quantum_oracle": OracleClassifier()}, r.convs, r.fc,
+                             snrs=(5, 15), n_per_pair=60, batch=60)
+    for a, b in zip(res["quantum"], res["quantum_oracle"]):
+        assert abs(a - b) < 0.05
+    assert res["acc_quantum"] == res["acc_quantum_oracle"]
+    assert all(np.isfinite(res["LS"]))
+
+
+@pytest.mark.parametrize("pilot", [32, 64, 256])
+def test_pilot_length_variants(pilot):
+    hw = D.pilot_shape(pilot)
+    model = E.QSC_P128(use_quantumnat=False, use_gradient_pruning=False, pilot_hw=hw).cuda()
+    gen = D.SyntheticRIS(pilot, seed=1, device="cuda")
+    yp, _, _, ind = gen.pair_set(2, 1, 24, 10.0, 3)
+    out = model(D.pilot_image(yp, pilot))
+    assert out.shape == (24, 3)
+    F.nll_loss(out, ind).backward()
+    assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in model.parameters())
