@@ -137,6 +137,42 @@ class QSC_P128(nn.Module):
             print(f"Gradient pruning: {n_pruned / total:.1%} gradients pruned")
 
 
+class QSC_QuantumNAT(nn.Module):
+    """north_star's on-chip QNN classifier (BASELINE config 3; not in the reference): the QSC front end
+    feeding a U3/CU3 circuit, with QuantumNAT weight noise (as Est:176-196) AND the post-measurement
+    normalise / noise / quantise head, then the linear classifier.  n_qubits = 10, 3 layers by default."""
+
+    def __init__(self, n_qubits=10, n_layers=3, n_classes=3, noise_level=0.01, act_noise=0.01, levels=5,
+                 quant_range=(-2.0, 2.0), pilot_hw=(16, 8), process_group=None):
+        super().__init__()
+        from .circuit import u3cu3_circuit
+        from .qlayer import QNNLayer
+        from .qnat import QuantumNATHead
+        self.num_qubits, self.n_classes, self.noise_level = n_qubits, n_classes, noise_level
+        self.qlayer = QNNLayer(u3cu3_circuit(n_qubits, n_layers), {"weights": (n_layers, 2, n_qubits, 3)})
+        self.preprocess = nn.Sequential(
+            nn.Conv2d(2, 16, 3, stride=1, padding=1), nn.ReLU(), nn.MaxPool2d(2),
+            nn.Conv2d(16, 32, 3, stride=1, padding=1), nn.ReLU(), nn.MaxPool2d(2),
+            nn.Flatten(), nn.Linear(32 * (pilot_hw[0] // 4) * (pilot_hw[1] // 4), n_qubits), nn.Tanh())
+        self.nat = QuantumNATHead(sigma=act_noise, lo=quant_range[0], hi=quant_range[1], levels=levels,
+                                  process_group=process_group)
+        self.classifier = nn.Linear(n_qubits, n_classes)
+
+    def forward(self, x):
+        angles = self.preprocess(x)
+        if self.training and self.noise_level > 0:
+            w = self.qlayer.weights
+            with torch.no_grad():
+                saved = w.data.clone()
+                w.data.add_(self.noise_level * torch.randn_like(w))
+            measured = self.qlayer(angles)
+            with torch.no_grad():
+                w.data.copy_(saved)
+        else:
+            measured = self.qlayer(angles)
+        return F.log_softmax(self.classifier(self.nat(measured)), dim=1)
+
+
 class Conv_P128(nn.Module):
     """HDCE feature extractor (Est:237-268): (B,2,16,8) -> (B,4096)."""
 

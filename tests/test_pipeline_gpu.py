@@ -132,3 +132,36 @@ def test_pilot_length_variants(pilot):
     assert out.shape == (24, 3)
     F.nll_loss(out, ind).backward()
     assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in model.parameters())
+
+
+def test_concatenated_users_step_equals_nine_way_step():
+    """one call on the concatenated user batches gives the same step as nine calls."""
+    r = runner.Y2HRunner(data_len=200, batch_size_DML=16, device="cuda", verbose=False)
+    torch.manual_seed(0)
+    m1 = E.QSC_P128(use_quantumnat=False, use_gradient_pruning=False).cuda().train()
+    m2 = copy.deepcopy(m1)
+    o1 = optim.FlatPrunedAdamW(m1.parameters(), lr=1e-3); o2 = optim.FlatPrunedAdamW(m2.parameters(), lr=1e-3)
+    sutd = next(iter(r.get_dataloader_DML()[0]))
+    l1 = r.qsc_step(m1, o1, sutd, concat_users=False); l2 = r.qsc_step(m2, o2, sutd, concat_users=True)
+    assert abs(l1.item() - l2.item()) < 1e-6
+    assert_close(o2.bucket.flat.cpu().numpy(), o1.bucket.flat.cpu().numpy(), rel=1e-5, scale=float(o1.bucket.flat.abs().max()), what="grads")
+
+
+def test_quantumnat_classifier_trains():
+    """BASELINE config 3's model: 10-qubit U3/CU3 QNN + weight noise + post-measurement QuantumNAT head."""
+    torch.manual_seed(0)
+    model = E.QSC_QuantumNAT().cuda().train()
+    assert model.qlayer.weights.shape == (3, 2, 10, 3)
+    gen = D.SyntheticRIS(128, seed=2, device="cuda")
+    opt = torch.optim.AdamW(model.parameters(), lr=5e-3)
+    losses = []
+    for it in range(12):
+        yp, ind = zip(*[(gen.pair_set(s, it % 3, 48, 10.0, it)[0], gen.pair_set(s, it % 3, 48, 10.0, it)[3]) for s in range(3)])
+        opt.zero_grad()
+        loss = F.nll_loss(model(D.pilot_image(torch.cat(yp), 128)), torch.cat(ind))
+        loss.backward(); opt.step(); losses.append(loss.item())
+    assert all(np.isfinite(losses)) and min(losses[-4:]) < losses[0]
+    model.eval()
+    with torch.no_grad():
+        out = model(D.pilot_image(gen.pair_set(0, 0, 32, 10.0, 99)[0], 128))
+    assert out.shape == (32, 3) and torch.isfinite(out).all()
