@@ -33,7 +33,9 @@ struct VmArgs {
   const float* coef; int n_coef;            // [n_coef][QNN_COEF_STRIDE] (workspace)
   const float2* big; int n_big;             // [n_big][1024]
   const float2* small; int n_small;         // [n_small][32]
-  int n, tb, n_inputs, n_acc;
+  int n, tb, wb, n_inputs, n_acc;           // tb = n - 5 thread bits; wb = warp bits (a group = 2^wb warps)
+  const uint32_t* xbase; int n_xbase;       // per-thread exchange bases
+  unsigned table_bytes;                     // shared-memory bytes of all tables (to place them around the buffers)
   unsigned skip_mask;                       // experiments only (QNN_VM_SKIP): micro-op kinds to skip
   int8_t wire_of_bit[16];                   // final (measurement) layout
   const float* x; float* y;                 // forward
@@ -287,13 +289,12 @@ __device__ __forceinline__ float warp_sum4(float t0, float t1, float t2, float t
 }
 
 // ---- exchange ---------------------------------------------------------------------------------------
-__device__ __forceinline__ void exchange(float2 (&st)[NA], uint32_t buf, const Exchange* X, int lane, bool reverse) {
-  const uint32_t* wbase = reverse ? X->rbase : X->wbase;
-  const uint32_t* woff = reverse ? X->roff : X->woff;
-  const uint32_t* rbase = reverse ? X->wbase : X->rbase;
-  const uint32_t* roff = reverse ? X->woff : X->roff;
-  const uint32_t wa = buf | wbase[lane], ra = buf | rbase[lane];
-  __syncwarp();
+// wa / ra: this thread's write / read base (buffer address | per-thread offset); `sync` is the barrier
+// of the group that shares the buffer (a warp for n <= 10, 2^wb warps above).
+template <typename Sync>
+__device__ __forceinline__ void exchange(float2 (&st)[NA], uint32_t wa, uint32_t ra, const uint32_t* woff,
+                                         const uint32_t* roff, Sync sync) {
+  sync();
 #pragma unroll
   for (int q = 0; q < NA / 4; ++q) {
     const uint4 o = *reinterpret_cast<const uint4*>(woff + 4 * q);
@@ -302,7 +303,7 @@ __device__ __forceinline__ void exchange(float2 (&st)[NA], uint32_t buf, const E
     sts64(wa ^ o.z, st[4 * q + 2].x, st[4 * q + 2].y);
     sts64(wa ^ o.w, st[4 * q + 3].x, st[4 * q + 3].y);
   }
-  __syncwarp();
+  sync();
 #pragma unroll
   for (int q = 0; q < NA / 4; ++q) {
     const uint4 o = *reinterpret_cast<const uint4*>(roff + 4 * q);
@@ -339,72 +340,95 @@ __device__ __forceinline__ float2 rot_coef_x(float xv) {
 struct Smem {
   MicroOp* ops;
   Exchange* exchanges;
+  uint32_t* xbase;
   DiagDesc* diags;
   float* coef;        // [n_coef][8]
-  float2* big;        // [n_big][1024]
+  const float2* big;  // [n_big][32 * G]: shared memory for n <= 10, the workspace (L2) above
   float2* small;      // [n_small][32]
   float* wacc;        // [warps][n_acc]        (backward)
   float* gxacc;       // [warps][spw * n_inputs]
-  float2* xcoef;      // [warps][spw * n_inputs]: shear coefficients of RY(x[b, col]), made once per warp-batch
-  uint32_t xbuf;      // shared address of this warp's 8 KB exchange buffer
+  float2* xcoef;      // [warps][spw * n_inputs]: shear coefficients of RY(x[b, col]), made once per batch
+  float* red;         // [groups][group warps][16]: cross-warp measurement partials (n > 10)
+  uint32_t xbuf;      // shared address of this group's exchange buffer (8 KB per warp, aligned to its size)
 };
 
-size_t smem_bytes(const Program& p, int n_inputs, int warps, bool bwd) {
-  size_t b = 8192;  // alignment slack for the exchange buffers
-  b += (size_t)warps * 8192;
-  b += p.ops.size() * sizeof(MicroOp);
-  b += p.exchanges.size() * sizeof(Exchange);
-  b += p.diags.size() * sizeof(DiagDesc);
-  b += p.coef_ops.size() * 8 * sizeof(float);
-  b += (size_t)p.n_big_tables * 1024 * sizeof(float2);
-  b += (size_t)p.n_small_tables * 32 * sizeof(float2);
-  b += (size_t)warps * (32 >> p.tb) * std::max(n_inputs, 1) * sizeof(float2);
+size_t table_bytes(const Program& p, int n_inputs, int warps, bool bwd) {
+  auto up = [](size_t v) { return (v + 15) & ~size_t(15); };
+  const int G = 32 << p.wb, spw = p.wb ? 1 : (32 >> p.tb);
+  size_t b = 0;
+  b += up(p.ops.size() * sizeof(MicroOp));
+  b += up(p.exchanges.size() * sizeof(Exchange));
+  b += up(p.xbase.size() * sizeof(uint32_t));
+  b += up(p.diags.size() * sizeof(DiagDesc));
+  b += up(p.coef_ops.size() * 8 * sizeof(float));
+  if (p.wb == 0) b += up((size_t)p.n_big_tables * 32 * G * sizeof(float2));
+  b += up((size_t)p.n_small_tables * 32 * sizeof(float2));
+  b += up((size_t)warps * spw * std::max(n_inputs, 1) * sizeof(float2));
+  b += up((size_t)warps * 16 * sizeof(float));
   if (bwd) {
-    b += (size_t)warps * std::max(p.n_acc, 1) * sizeof(float);
-    b += (size_t)warps * (32 >> p.tb) * std::max(n_inputs, 1) * sizeof(float);
+    b += up((size_t)warps * std::max(p.n_acc, 1) * sizeof(float));
+    b += up((size_t)warps * spw * std::max(n_inputs, 1) * sizeof(float));
   }
-  return b + 256;  // per-array 16-byte alignment slack
+  return b;
+}
+// exchange buffers (8 KB per warp, each group's aligned to its size) + worst-case alignment gap + tables
+size_t smem_bytes(const Program& p, int n_inputs, int warps, bool bwd) {
+  const size_t group_buf = (size_t)8192 << p.wb;
+  return group_buf + (size_t)warps * 8192 + table_bytes(p, n_inputs, warps, bwd) + 64;
 }
 
-template <bool BWD, int THREADS, int MINB, bool STATE>
+// MW: a sample spans several warps (n > 10).  MW = false compiles the single-warp geometry with constant
+// strides and __syncwarp barriers.
+template <bool BWD, int THREADS, int MINB, bool STATE, bool MW>
 __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   constexpr int WARPS = THREADS / 32;
-  const int tb = a.tb, T = 1 << tb, spw = 32 >> tb;
-  const int lis = lane & (T - 1), siw = lane >> tb;
+  const int tb = a.tb, wbits = MW ? a.wb : 0;
+  const int gwarps = 1 << wbits, G = 32 << wbits;          // warps / threads per group (one sample for n >= 10)
+  const int gw = warp & (gwarps - 1), grp = warp >> wbits, groups = WARPS >> wbits;
+  const int spw = wbits ? 1 : (32 >> tb);                  // samples per warp (n <= 10)
+  const int tig = (gw << 5) | lane;                        // thread in group
+  const int tis = wbits ? tig : (lane & ((1 << tb) - 1));  // thread in sample: the sample's thread bits
+  const int siw = wbits ? 0 : (lane >> tb);                // sample in warp
+  const int lbits = tb < 5 ? tb : 5;                       // thread bits that are lanes of this warp
 
-  // ---- carve shared memory: exchange buffers first (8 KB aligned), then the tables -------------
+  // ---- carve shared memory: group exchange buffers (aligned to their size); tables go into the
+  //      alignment gap below them when they fit, else behind them ------------------------------------
   Smem S;
   {
     const uint32_t s0 = (uint32_t)__cvta_generic_to_shared(smem_raw);
-    const uint32_t xb = (s0 + 8191u) & ~8191u;
-    S.xbuf = xb + (uint32_t)warp * 8192u;
-    unsigned char* p = smem_raw + (xb - s0) + (size_t)WARPS * 8192;
+    const uint32_t gbuf = 8192u << wbits;
+    const uint32_t xb = (s0 + gbuf - 1u) & ~(gbuf - 1u);
+    S.xbuf = xb + (uint32_t)grp * gbuf;
+    const size_t tables = a.table_bytes;
+    unsigned char* p = (xb - s0 >= tables) ? smem_raw : smem_raw + (xb - s0) + (size_t)WARPS * 8192;
     auto take = [&](size_t bytes) { unsigned char* r = p; p += (bytes + 15) & ~size_t(15); return r; };
     S.ops = reinterpret_cast<MicroOp*>(take((size_t)a.n_ops * sizeof(MicroOp)));
     S.exchanges = reinterpret_cast<Exchange*>(take((size_t)a.n_exchanges * sizeof(Exchange)));
+    S.xbase = reinterpret_cast<uint32_t*>(take((size_t)a.n_xbase * sizeof(uint32_t)));
     S.diags = reinterpret_cast<DiagDesc*>(take((size_t)a.n_diags * sizeof(DiagDesc)));
     S.coef = reinterpret_cast<float*>(take((size_t)a.n_coef * 8 * sizeof(float)));
-    S.big = reinterpret_cast<float2*>(take((size_t)a.n_big * 1024 * sizeof(float2)));
+    float2* sbig = wbits == 0 ? reinterpret_cast<float2*>(take((size_t)a.n_big * 32 * G * sizeof(float2))) : nullptr;
+    S.big = wbits == 0 ? sbig : a.big;
     S.small = reinterpret_cast<float2*>(take((size_t)a.n_small * 32 * sizeof(float2)));
     S.xcoef = reinterpret_cast<float2*>(take((size_t)WARPS * spw * max(a.n_inputs, 1) * sizeof(float2)));
+    S.red = reinterpret_cast<float*>(take((size_t)WARPS * 16 * sizeof(float)));
     if (BWD) {
       S.wacc = reinterpret_cast<float*>(take((size_t)WARPS * max(a.n_acc, 1) * sizeof(float)));
       S.gxacc = reinterpret_cast<float*>(take((size_t)WARPS * spw * max(a.n_inputs, 1) * sizeof(float)));
     }
-  }
-  {
     const int tid = threadIdx.x;
     const uint32_t* src; uint32_t* dst; int words;
     src = reinterpret_cast<const uint32_t*>(a.ops); dst = reinterpret_cast<uint32_t*>(S.ops); words = a.n_ops * (int)(sizeof(MicroOp) / 4);
     for (int i = tid; i < words; i += THREADS) dst[i] = src[i];
     src = reinterpret_cast<const uint32_t*>(a.exchanges); dst = reinterpret_cast<uint32_t*>(S.exchanges); words = a.n_exchanges * (int)(sizeof(Exchange) / 4);
     for (int i = tid; i < words; i += THREADS) dst[i] = src[i];
+    for (int i = tid; i < a.n_xbase; i += THREADS) S.xbase[i] = a.xbase[i];
     src = reinterpret_cast<const uint32_t*>(a.diags); dst = reinterpret_cast<uint32_t*>(S.diags); words = a.n_diags * (int)(sizeof(DiagDesc) / 4);
     for (int i = tid; i < words; i += THREADS) dst[i] = src[i];
     for (int i = tid; i < a.n_coef * 8; i += THREADS) S.coef[i] = a.coef[(size_t)(i >> 3) * QNN_COEF_STRIDE + (i & 7)];
-    for (int i = tid; i < a.n_big * 1024; i += THREADS) S.big[i] = a.big[i];
+    if (wbits == 0) for (int i = tid; i < a.n_big * 32 * G; i += THREADS) sbig[i] = a.big[i];
     for (int i = tid; i < a.n_small * 32; i += THREADS) S.small[i] = a.small[i];
     if (BWD) {
       for (int i = tid; i < WARPS * max(a.n_acc, 1); i += THREADS) S.wacc[i] = 0.f;
@@ -414,16 +438,22 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
   __syncthreads();
   float* const wacc = BWD ? S.wacc + (size_t)warp * max(a.n_acc, 1) : nullptr;
   float* const gxacc = BWD ? S.gxacc + (size_t)warp * spw * max(a.n_inputs, 1) : nullptr;
+  float* const red = S.red + (size_t)warp * 16;
+  // barrier over the threads that share one exchange buffer
+  auto gsync = [&]() {
+    if constexpr (!MW) __syncwarp();
+    else asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "r"(G) : "memory");
+  };
 
   float2* const xcoef = S.xcoef + (size_t)warp * spw * max(a.n_inputs, 1);
   float2 ps[NA];
   const long long n_batches = (a.B + spw - 1) / spw;
-  for (long long wb = (long long)blockIdx.x * WARPS + warp; wb < n_batches; wb += (long long)gridDim.x * WARPS) {
+  for (long long wb = (long long)blockIdx.x * groups + grp; wb < n_batches; wb += (long long)gridDim.x * groups) {
     const long long bs = wb * spw + siw;
     const bool active = bs < a.B;
+    gsync();   // nothing of the previous batch (scratch, exchange buffer) is still being read
 
     // shear coefficients of the per-sample rotations RY(x[b, col]): each (sample, column) once per batch
-    __syncwarp();
     for (int i = lane; i < spw * a.n_inputs; i += 32) {
       const long long bb = wb * spw + i / a.n_inputs;
       xcoef[i] = rot_coef_x(bb < a.B ? a.x[(size_t)bb * a.n_inputs + (i % a.n_inputs)] : 0.f);
@@ -433,17 +463,17 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
 
     // Saved final state: [batch][j / 2][lane] float4 = amplitudes (2 * (j/2), 2 * (j/2) + 1) of that lane;
     // a warp reads or writes 512 contiguous bytes per instruction.
-    float4* const st_rows = STATE ? a.state + (size_t)wb * (NA / 2) * 32 + lane : nullptr;
+    float4* const st_rows = STATE ? a.state + (size_t)wb * (NA / 2) * G + tig : nullptr;
     if constexpr (BWD && STATE) {
 #pragma unroll
       for (int q = 0; q < NA / 2; ++q) {
-        const float4 v = __ldcs(st_rows + q * 32);
+        const float4 v = __ldcs(st_rows + (size_t)q * G);
         ps[2 * q] = make_float2(v.x, v.y); ps[2 * q + 1] = make_float2(v.z, v.w);
       }
     } else {
 #pragma unroll
     for (int j = 0; j < NA; ++j) ps[j] = make_float2(0.f, 0.f);
-    ps[0].x = lis == 0 ? 1.f : 0.f;
+    ps[0].x = tis == 0 ? 1.f : 0.f;
 
     // ================= forward program =================
     // One jump per micro-op (handler id = kind and register bits); the next op and its coefficient row
@@ -469,7 +499,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
           H_CASE_CU3L(3, 0) H_CASE_CU3L(3, 1) H_CASE_CU3L(3, 2) H_CASE_CU3L(3, 4)
           H_CASE_CU3L(4, 0) H_CASE_CU3L(4, 1) H_CASE_CU3L(4, 2) H_CASE_CU3L(4, 3)
 #undef H_CASE_CU3L
-#define H_CASE_CU3P(RB) case H_CU3P + RB: if (__popc(lis & op.aux) & 1) { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_all<RB>(ps, g); } break;
+#define H_CASE_CU3P(RB) case H_CU3P + RB: if (__popc(tis & op.aux) & 1) { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_all<RB>(ps, g); } break;
           H_CASE_CU3P(0) H_CASE_CU3P(1) H_CASE_CU3P(2) H_CASE_CU3P(3) H_CASE_CU3P(4)
 #undef H_CASE_CU3P
           case H_ROT5: {
@@ -492,9 +522,12 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
             { const Cu3 g = load_cu3(S.coef + (op.idx + 2) * 8, false); cu3_loc<3, 2>(ps, g); }
             { const Cu3 g = load_cu3(S.coef + (op.idx + 3) * 8, false); cu3_loc<4, 3>(ps, g); }
           } break;
-          case H_DIAG: diag_mul<false, false>(ps, ps, S.big + op.idx * 1024, 32, lane); break;
+          case H_DIAG: diag_mul<false, false>(ps, ps, S.big + (size_t)op.idx * 32 * G, G, tig); break;
           case H_DIAGR: diag_mul<false, false>(ps, ps, S.small + op.idx * 32, 1, 0); break;
-          case H_XCHG: exchange(ps, S.xbuf, S.exchanges + op.idx, lane, false); break;
+          case H_XCHG: {
+            const Exchange* X = S.exchanges + op.idx;
+            exchange(ps, S.xbuf | S.xbase[X->base + tig], S.xbuf | S.xbase[X->base + G + tig], X->woff, X->roff, gsync);
+          } break;
           default: break;
         }
         op = next;
@@ -506,7 +539,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
     if constexpr (!BWD && STATE) {
 #pragma unroll
       for (int q = 0; q < NA / 2; ++q)
-        __stcs(st_rows + q * 32, make_float4(ps[2 * q].x, ps[2 * q].y, ps[2 * q + 1].x, ps[2 * q + 1].y));
+        __stcs(st_rows + (size_t)q * G, make_float4(ps[2 * q].x, ps[2 * q].y, ps[2 * q + 1].x, ps[2 * q + 1].y));
     }
 
     if constexpr (!BWD) {
@@ -514,28 +547,49 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
       float2 tot2, S2[kR];
       signed_sums2([&](int j) { return __fmul2_rn(ps[j], ps[j]); }, tot2, S2);
       const float tot = tot2.x + tot2.y;
-      float val[10];
+      // per-warp partials: [0..4] register bits, [5..9] lane bits, [10] plain total (for the warp bits)
+      float val[11];
 #pragma unroll
-      for (int r = 0; r < kR; ++r) val[r] = sample_sum(S2[r].x + S2[r].y, tb);
+      for (int r = 0; r < kR; ++r) val[r] = sample_sum(S2[r].x + S2[r].y, lbits);
 #pragma unroll
-      for (int b = 0; b < 5; ++b) val[kR + b] = (b < tb) ? sample_sum(((lis >> b) & 1) ? -tot : tot, tb) : 0.f;
-      if (active && lis == 0) {
-        float* yrow = a.y + (size_t)bs * a.n;
+      for (int b = 0; b < 5; ++b) val[kR + b] = (b < lbits) ? sample_sum(((lane >> b) & 1) ? -tot : tot, lbits) : 0.f;
+      val[10] = sample_sum(tot, lbits);
+      if (wbits == 0) {
+        if (active && tis == 0) {
+          float* yrow = a.y + (size_t)bs * a.n;
 #pragma unroll
-        for (int pb = 0; pb < 10; ++pb)
-          if (pb < a.n) yrow[a.wire_of_bit[pb]] = val[pb];
+          for (int pb = 0; pb < 10; ++pb)
+            if (pb < a.n) yrow[a.wire_of_bit[pb]] = val[pb];
+        }
+      } else {
+        // a sample spans 2^wb warps: combine their partials through shared memory (fixed order)
+        if (lane == 0) {
+#pragma unroll
+          for (int c = 0; c < 11; ++c) red[c] = val[c];
+        }
+        gsync();
+        if (gw == 0 && lane < a.n && active) {
+          const float* r0 = S.red + (size_t)(grp << wbits) * 16;
+          float t = 0.f;
+          if (lane < 10) {
+            for (int w = 0; w < gwarps; ++w) t += r0[w * 16 + lane];
+          } else {
+            for (int w = 0; w < gwarps; ++w) t += ((w >> (lane - 10)) & 1) ? -r0[w * 16 + 10] : r0[w * 16 + 10];
+          }
+          a.y[(size_t)bs * a.n + a.wire_of_bit[lane]] = t;
+        }
       }
     } else {
       // ================= seed lam = (sum_q gy_q Z_q) psi =================
       float2 ls[NA];
       {
-        float g[10];
+        float g[kR + kMaxThreadBits];
         const float* gyrow = a.gy + (size_t)(active ? bs : 0) * a.n;
 #pragma unroll
-        for (int pb = 0; pb < 10; ++pb) g[pb] = (active && pb < a.n) ? gyrow[a.wire_of_bit[pb]] : 0.f;
+        for (int pb = 0; pb < kR + kMaxThreadBits; ++pb) g[pb] = (active && pb < a.n) ? gyrow[a.wire_of_bit[pb]] : 0.f;
         float cl = 0.f;
 #pragma unroll
-        for (int b = 0; b < 5; ++b) cl += ((lis >> b) & 1) ? -g[kR + b] : g[kR + b];
+        for (int b = 0; b < kMaxThreadBits; ++b) cl += ((tis >> b) & 1) ? -g[kR + b] : g[kR + b];
         float cj[NA];
         cj[0] = cl + g[0] + g[1] + g[2] + g[3] + g[4];
 #pragma unroll
@@ -560,7 +614,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
           H_CASE_ROT(0) H_CASE_ROT(1) H_CASE_ROT(2) H_CASE_ROT(3) H_CASE_ROT(4)
 #undef H_CASE_ROT
 #define H_CASE_ROTX(RB) case H_ROTX + RB: { const float2 ab = xc[op.idx]; float v = rot_grad<RB>(ps, ls); rot<RB>(ps, -ab.x, -ab.y); rot<RB>(ls, -ab.x, -ab.y); \
-            v = sample_sum(v, tb); if (lis == 0) gxacc[siw * a.n_inputs + op.idx] += v; } break;
+            v = sample_sum(v, lbits); if ((lane & ((1 << lbits) - 1)) == 0) gxacc[siw * a.n_inputs + op.idx] += v; } break;
           H_CASE_ROTX(0) H_CASE_ROTX(1) H_CASE_ROTX(2) H_CASE_ROTX(3) H_CASE_ROTX(4)
 #undef H_CASE_ROTX
 #define CU3_REDUCE(A, ACC)                                                                                  \
@@ -578,7 +632,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
           H_CASE_CU3L(4, 0) H_CASE_CU3L(4, 1) H_CASE_CU3L(4, 2) H_CASE_CU3L(4, 3)
 #undef H_CASE_CU3L
 #define H_CASE_CU3P(RB) case H_CU3P + RB: { const float2 z = make_float2(0.f, 0.f); Cu3Acc A{z, z, z, z}; \
-            if (__popc(lis & op.aux) & 1) { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), true); cu3_all_bwd<RB>(ps, ls, g, A); } \
+            if (__popc(tis & op.aux) & 1) { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), true); cu3_all_bwd<RB>(ps, ls, g, A); } \
             CU3_REDUCE(A, op.acc) } break;
           H_CASE_CU3P(0) H_CASE_CU3P(1) H_CASE_CU3P(2) H_CASE_CU3P(3) H_CASE_CU3P(4)
 #undef H_CASE_CU3P
@@ -605,8 +659,8 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
               const float2 ab = xc[col];                                                                   \
               float v = rot_grad<K>(ps, ls);                                                               \
               rot<K>(ps, -ab.x, -ab.y); rot<K>(ls, -ab.x, -ab.y);                                          \
-              v = sample_sum(v, tb);                                                                       \
-              if (lis == 0) gxacc[siw * a.n_inputs + col] += v;                                            \
+              v = sample_sum(v, lbits);                                                                    \
+              if ((lane & ((1 << lbits) - 1)) == 0) gxacc[siw * a.n_inputs + col] += v;                    \
             }
             ROTX5_STEP(4) ROTX5_STEP(3) ROTX5_STEP(2) ROTX5_STEP(1) ROTX5_STEP(0)
 #undef ROTX5_STEP
@@ -639,37 +693,42 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
 #pragma unroll
             for (int r = 0; r < kR; ++r) t16[r] = S2[r].x - S2[r].y;
 #pragma unroll
-            for (int b = 0; b < 5; ++b) t16[kR + b] = ((lis >> b) & 1) ? -tot : tot;
+            for (int b = 0; b < kMaxThreadBits; ++b) t16[kR + b] = ((tis >> b) & 1) ? -tot : tot;
 #pragma unroll
-            for (int k = 10; k < 16; ++k) t16[k] = 0.f;
+            for (int k = kR + kMaxThreadBits; k < 16; ++k) t16[k] = 0.f;
             const float r = warp_sum16(t16, lane);
             if ((lane & 1) == 0) {
               const int comp = lane >> 1;
-              const int ai = comp < kR ? D->acc_reg[comp] : (comp < 10 && op.pad0 == H_DIAG ? D->acc_lane[comp - kR] : -1);
+              const int ai = comp < kR ? D->acc_reg[comp]
+                                       : (comp < kR + kMaxThreadBits && op.pad0 == H_DIAG ? D->acc_thr[comp - kR] : -1);
               if (ai >= 0) wacc[ai] += r;
             }
-            if (op.pad0 == H_DIAG) diag_mul<true, true>(ps, ls, S.big + op.idx * 1024, 32, lane);
+            if (op.pad0 == H_DIAG) diag_mul<true, true>(ps, ls, S.big + (size_t)op.idx * 32 * G, G, tig);
             else diag_mul<true, true>(ps, ls, S.small + op.idx * 32, 1, 0);
           } break;
-          case H_XCHG:
-            exchange(ps, S.xbuf, S.exchanges + op.idx, lane, true);
-            exchange(ls, S.xbuf, S.exchanges + op.idx, lane, true);
-            break;
+          case H_XCHG: {   // inverse: roles of the two address sets swapped
+            const Exchange* X = S.exchanges + op.idx;
+            const uint32_t wa = S.xbuf | S.xbase[X->base + G + tig], ra = S.xbuf | S.xbase[X->base + tig];
+            exchange(ps, wa, ra, X->roff, X->woff, gsync);
+            exchange(ls, wa, ra, X->roff, X->woff, gsync);
+          } break;
           default: break;
         }
         op = next;
         cfa = ncfa;
       }
-      // ================= input gradients of this warp's samples =================
-      __syncwarp();
-      if (a.gx != nullptr) {
+      // ================= input gradients of this group's samples =================
+      gsync();
+      if (a.gx != nullptr && gw == 0) {
         for (int i = lane; i < spw * a.n_inputs; i += 32) {
           const long long bb = wb * spw + i / a.n_inputs;
-          if (bb < a.B) a.gx[(size_t)bb * a.n_inputs + (i % a.n_inputs)] = gxacc[i];
+          float t = 0.f;
+          for (int w = 0; w < gwarps; ++w) t += gxacc[(size_t)w * spw * max(a.n_inputs, 1) + i];   // the group's warps, fixed order
+          if (bb < a.B) a.gx[(size_t)bb * a.n_inputs + (i % a.n_inputs)] = t;
         }
       }
+      gsync();
       for (int i = lane; i < spw * a.n_inputs; i += 32) gxacc[i] = 0.f;
-      __syncwarp();
     }
   }
 
@@ -686,7 +745,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
 
 // ---- per-call tables: gate coefficients (double-precision trig) and merged diagonals -----------------
 __global__ void k_vm_prep(const DevOp* __restrict__ coef_ops, int n_coef, const DiagDesc* __restrict__ diags, int n_diags,
-                          const DiagTerm* __restrict__ terms, const float* __restrict__ w, int tb, float* __restrict__ coef,
+                          const DiagTerm* __restrict__ terms, const float* __restrict__ w, int tb, int wbits, float* __restrict__ coef,
                           float2* __restrict__ big, float2* __restrict__ small, int coef_blocks) {
   if ((int)blockIdx.x < coef_blocks) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -713,11 +772,12 @@ __global__ void k_vm_prep(const DevOp* __restrict__ coef_ops, int n_coef, const 
   const int d = blockIdx.x - coef_blocks;
   if (d >= n_diags) return;
   const DiagDesc D = diags[d];
-  const int entries = D.is_reg ? 32 : 1024;
-  const int T = 1 << tb;
+  const int G = 32 << wbits;
+  const int entries = D.is_reg ? 32 : 32 * G;
+  const unsigned tmask = wbits ? (unsigned)(G - 1) : ((1u << tb) - 1u);   // thread bits of one sample
   for (int e = threadIdx.x; e < entries; e += blockDim.x) {
-    const int j = D.is_reg ? e : (e >> 5), lane = D.is_reg ? 0 : (e & 31);
-    const unsigned p = (unsigned)j | ((unsigned)(lane & (T - 1)) << kR);
+    const int j = D.is_reg ? e : (e / G), t = D.is_reg ? 0 : (e % G);
+    const unsigned p = (unsigned)j | (((unsigned)t & tmask) << kR);
     double ang = 0.0;
     for (int t = 0; t < D.n_terms; ++t) {
       const DiagTerm tm = terms[D.first_term + t];
@@ -731,7 +791,7 @@ __global__ void k_vm_prep(const DevOp* __restrict__ coef_ops, int n_coef, const 
     double s, c;
     sincos(ang, &s, &c);
     const float2 v = make_float2((float)c, (float)s);
-    if (D.is_reg) small[(size_t)D.table * 32 + e] = v; else big[(size_t)D.table * 1024 + e] = v;
+    if (D.is_reg) small[(size_t)D.table * 32 + e] = v; else big[(size_t)D.table * 32 * G + e] = v;
   }
 }
 
@@ -758,19 +818,7 @@ __global__ void k_vm_finalize(const float* __restrict__ partial, int n_ctas, int
 size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
 
 constexpr size_t kSmemMax = 227 * 1024;
-
-struct Variant { int fwd_threads, bwd_threads; };
-Variant variant() {
-  static Variant v = [] {
-    Variant r{512, 256};
-    if (const char* e = getenv("QNN_VM_VARIANT")) {   // tuning knob: "<fwd threads>,<bwd threads>"
-      int a = 0, b = 0;
-      if (sscanf(e, "%d,%d", &a, &b) == 2 && (a == 256 || a == 512) && (b == 256 || b == 384)) { r.fwd_threads = a; r.bwd_threads = b; }
-    }
-    return r;
-  }();
-  return v;
-}
+constexpr int kFwdThreads = 512, kBwdThreads = 256;   // 16 / 8 warps per CTA, one CTA per SM (124 / 231 registers)
 
 template <typename K>
 int set_smem(K kern, size_t bytes) {
@@ -778,15 +826,18 @@ int set_smem(K kern, size_t bytes) {
   return QNN_OK;
 }
 
-void fill_args(const qnn_circuit* c, const Program& p, const Plan& pl, void* ws, VmArgs* a) {
+void fill_args(const qnn_circuit* c, const Program& p, const Plan& pl, void* ws, bool bwd, VmArgs* a) {
   unsigned char* wsb = static_cast<unsigned char*>(ws);
+  const size_t G = (size_t)32 << p.wb;
   a->ops = p.d_ops; a->n_ops = (int)p.ops.size();
   a->exchanges = p.d_exchanges; a->n_exchanges = (int)p.exchanges.size();
+  a->xbase = p.d_xbase; a->n_xbase = (int)p.xbase.size();
   a->diags = p.d_diags; a->n_diags = (int)p.diags.size();
   a->coef = reinterpret_cast<const float*>(wsb); a->n_coef = (int)p.coef_ops.size();
   a->big = reinterpret_cast<const float2*>(wsb + pl.ws_coef); a->n_big = p.n_big_tables;
-  a->small = a->big + (size_t)p.n_big_tables * 1024; a->n_small = p.n_small_tables;
-  a->n = p.n; a->tb = p.tb; a->n_inputs = c->n_inputs; a->n_acc = p.n_acc;
+  a->small = a->big + (size_t)p.n_big_tables * 32 * G; a->n_small = p.n_small_tables;
+  a->n = p.n; a->tb = p.tb; a->wb = p.wb; a->n_inputs = c->n_inputs; a->n_acc = p.n_acc;
+  a->table_bytes = (unsigned)table_bytes(p, c->n_inputs, (bwd ? kBwdThreads : kFwdThreads) / 32, bwd);
   { const char* e = getenv("QNN_VM_SKIP"); a->skip_mask = e ? (unsigned)strtoul(e, nullptr, 0) : 0u; }
   for (int b = 0; b < 16; ++b) a->wire_of_bit[b] = 0;
   for (int w = 0; w < p.n; ++w) a->wire_of_bit[p.final_bit_of_wire[w]] = (int8_t)w;
@@ -797,7 +848,7 @@ int launch_prep(const Program& p, const float* w, const VmArgs& a, cudaStream_t 
   const int coef_blocks = ((int)p.coef_ops.size() + 127) / 128;
   const int blocks = coef_blocks + (int)p.diags.size();
   if (blocks == 0) return QNN_OK;
-  k_vm_prep<<<blocks, 128, 0, st>>>(p.d_coef_ops, (int)p.coef_ops.size(), p.d_diags, (int)p.diags.size(), p.d_terms, w, p.tb,
+  k_vm_prep<<<blocks, 128, 0, st>>>(p.d_coef_ops, (int)p.coef_ops.size(), p.d_diags, (int)p.diags.size(), p.d_terms, w, p.tb, p.wb,
                                     const_cast<float*>(a.coef), const_cast<float2*>(a.big), const_cast<float2*>(a.small),
                                     coef_blocks);
   QNN_CUDA_CHECK(cudaGetLastError());
@@ -806,26 +857,35 @@ int launch_prep(const Program& p, const float* w, const VmArgs& a, cudaStream_t 
 
 }  // namespace
 
+static int64_t n_batches(const Program& p, int64_t B) {
+  const int64_t spw = p.wb ? 1 : (32 >> p.tb);
+  return (B + spw - 1) / spw;
+}
+
 size_t state_bytes(const Program& p, int64_t B) {
-  const int64_t spw = 32 >> p.tb;
-  return (size_t)((B + spw - 1) / spw) * kWarpAmps * sizeof(float2);
+  return (size_t)n_batches(p, B) * ((size_t)kWarpAmps << p.wb) * sizeof(float2);
 }
 
 bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
   if (!p.ok) return false;
-  const Variant v = variant();
-  const size_t sf = smem_bytes(p, c->n_inputs, v.fwd_threads / 32, false);
-  const size_t sb = smem_bytes(p, c->n_inputs, v.bwd_threads / 32, true);
+  if ((kBwdThreads / 32) >> p.wb == 0) return false;            // a sample must fit the warps of one CTA
+  out->fwd_threads = kFwdThreads;
+  size_t sf = smem_bytes(p, c->n_inputs, kFwdThreads / 32, false);
+  if (sf > kSmemMax && p.wb > 0) {                               // large samples: fewer groups per CTA
+    out->fwd_threads = kBwdThreads;
+    sf = smem_bytes(p, c->n_inputs, kBwdThreads / 32, false);
+  }
+  const size_t sb = smem_bytes(p, c->n_inputs, kBwdThreads / 32, true);
   if (sf > kSmemMax || sb > kSmemMax) return false;
-  out->threads = v.bwd_threads;
-  out->warps_per_cta = v.bwd_threads / 32;
+  out->threads = kBwdThreads;
+  out->warps_per_cta = kBwdThreads / 32;
   out->smem_fwd = sf;
   out->smem_bwd = sb;
-  const int64_t batches = (B + (32 >> p.tb) - 1) / (32 >> p.tb);
-  const int64_t ctas = (batches + out->warps_per_cta - 1) / out->warps_per_cta;
+  const int64_t groups_per_cta = (kBwdThreads / 32) >> p.wb;
+  const int64_t ctas = (n_batches(p, B) + groups_per_cta - 1) / groups_per_cta;
   out->grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, 148));   // backward: one CTA per SM
   out->ws_coef = align256(std::max<size_t>(p.coef_ops.size(), 1) * QNN_COEF_STRIDE * sizeof(float));
-  out->ws_diag = align256(((size_t)p.n_big_tables * 1024 + (size_t)p.n_small_tables * 32 + 1) * sizeof(float2));
+  out->ws_diag = align256(((size_t)p.n_big_tables * (1024u << p.wb) + (size_t)p.n_small_tables * 32 + 1) * sizeof(float2));
   out->ws_partial = align256((size_t)out->grid * std::max(p.n_acc, 1) * sizeof(float));
   return true;
 }
@@ -844,6 +904,7 @@ int upload(Program* p, int n_weights) {
   if ((rc = up((void**)&p->d_terms, p->terms.data(), p->terms.size() * sizeof(DiagTerm)))) return rc;
   if ((rc = up((void**)&p->d_diags, p->diags.data(), p->diags.size() * sizeof(DiagDesc)))) return rc;
   if ((rc = up((void**)&p->d_exchanges, p->exchanges.data(), p->exchanges.size() * sizeof(Exchange)))) return rc;
+  if ((rc = up((void**)&p->d_xbase, p->xbase.data(), p->xbase.size() * sizeof(uint32_t)))) return rc;
   if ((rc = up((void**)&p->d_slots, p->slots.data(), p->slots.size() * sizeof(GradSlot)))) return rc;
   return upload_csr(p, n_weights);
 }
@@ -863,55 +924,52 @@ static int upload_csr(Program* p, int n_weights) {
 }
 
 void release(Program* p) {
-  for (void* d : {(void*)p->d_ops, (void*)p->d_coef_ops, (void*)p->d_terms, (void*)p->d_diags, (void*)p->d_exchanges,
+  for (void* d : {(void*)p->d_ops, (void*)p->d_coef_ops, (void*)p->d_terms, (void*)p->d_diags, (void*)p->d_exchanges, (void*)p->d_xbase,
                   (void*)p->d_slots, (void*)p->d_slot_ptr, (void*)p->d_slot_idx})
     if (d) cudaFree(d);
   p->d_ops = nullptr; p->d_coef_ops = nullptr; p->d_terms = nullptr; p->d_diags = nullptr;
-  p->d_exchanges = nullptr; p->d_slots = nullptr; p->d_slot_ptr = nullptr; p->d_slot_idx = nullptr;
+  p->d_exchanges = nullptr; p->d_xbase = nullptr; p->d_slots = nullptr; p->d_slot_ptr = nullptr; p->d_slot_idx = nullptr;
 }
 
 int forward(const qnn_circuit* c, const Program& p, const Plan& pl, const float* x, const float* w, float* y,
             int64_t B, void* ws, float* state, cudaStream_t st) {
   VmArgs a{};
-  fill_args(c, p, pl, ws, &a);
+  fill_args(c, p, pl, ws, false, &a);
+  a.table_bytes = (unsigned)table_bytes(p, c->n_inputs, pl.fwd_threads / 32, false);
   a.x = x; a.y = y; a.B = B; a.state = reinterpret_cast<float4*>(state);
   int rc = launch_prep(p, w, a, st);
   if (rc) return rc;
-  const Variant v = variant();
-  const int spw = 32 >> p.tb, wpc = v.fwd_threads / 32;
-  const int64_t ctas = ((B + spw - 1) / spw + wpc - 1) / wpc;
-  auto go = [&](auto kern, int minb) -> int {
+  const int64_t groups_per_cta = (pl.fwd_threads / 32) >> p.wb;
+  const int64_t ctas = (n_batches(p, B) + groups_per_cta - 1) / groups_per_cta;
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, 148));
+  auto go = [&](auto kern, int threads) -> int {
     int r = set_smem(kern, pl.smem_fwd);
     if (r) return r;
-    const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(minb, kSmemMax / pl.smem_fwd));
-    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, 148 * per_sm));
-    kern<<<grid, v.fwd_threads, pl.smem_fwd, st>>>(a);
+    kern<<<grid, threads, pl.smem_fwd, st>>>(a);
     QNN_CUDA_CHECK(cudaGetLastError());
     return QNN_OK;
   };
-  if (a.state) return v.fwd_threads == 512 ? go(k_vm<false, 512, 1, true>, 1) : go(k_vm<false, 256, 2, true>, 2);
-  if (v.fwd_threads == 512) return go(k_vm<false, 512, 1, false>, 1);
-  return go(k_vm<false, 256, 2, false>, 2);
+  if (p.wb == 0) return a.state ? go(k_vm<false, kFwdThreads, 1, true, false>, kFwdThreads) : go(k_vm<false, kFwdThreads, 1, false, false>, kFwdThreads);
+  if (pl.fwd_threads == kFwdThreads) return a.state ? go(k_vm<false, kFwdThreads, 1, true, true>, kFwdThreads) : go(k_vm<false, kFwdThreads, 1, false, true>, kFwdThreads);
+  return a.state ? go(k_vm<false, kBwdThreads, 1, true, true>, kBwdThreads) : go(k_vm<false, kBwdThreads, 1, false, true>, kBwdThreads);
 }
 
 int backward(const qnn_circuit* c, const Program& p, const Plan& pl, const float* x, const float* w,
              const float* gy, float* gx, float* gw, int64_t B, void* ws, const float* state, cudaStream_t st) {
   VmArgs a{};
-  fill_args(c, p, pl, ws, &a);
+  fill_args(c, p, pl, ws, true, &a);
   a.x = x; a.gy = gy; a.gx = gx; a.B = B; a.state = reinterpret_cast<float4*>(const_cast<float*>(state));
   int rc = launch_prep(p, w, a, st);
   if (rc) return rc;
-  const Variant v = variant();
   auto go = [&](auto kern) -> int {
     int r = set_smem(kern, pl.smem_bwd);
     if (r) return r;
-    kern<<<pl.grid, v.bwd_threads, pl.smem_bwd, st>>>(a);
+    kern<<<pl.grid, kBwdThreads, pl.smem_bwd, st>>>(a);
     QNN_CUDA_CHECK(cudaGetLastError());
     return QNN_OK;
   };
-  if (a.state) rc = go(k_vm<true, 256, 1, true>);
-  else if (v.bwd_threads == 384) rc = go(k_vm<true, 384, 1, false>);
-  else rc = go(k_vm<true, 256, 1, false>);
+  if (p.wb == 0) rc = a.state ? go(k_vm<true, kBwdThreads, 1, true, false>) : go(k_vm<true, kBwdThreads, 1, false, false>);
+  else rc = a.state ? go(k_vm<true, kBwdThreads, 1, true, true>) : go(k_vm<true, kBwdThreads, 1, false, true>);
   if (rc) return rc;
   if (c->n_weights > 0) {
     k_vm_finalize<<<c->n_weights, 128, 0, st>>>(a.partial, pl.grid, p.n_acc, p.d_slots, p.d_slot_ptr, p.d_slot_idx, gw);

@@ -2,8 +2,9 @@
 // and the kernels (qnn_vm.cu).
 //
 // Geometry: every thread keeps 2^R = 32 complex amplitudes of one sample in registers (R = 5 "register
-// bits"); 2^TB lanes of a warp share a sample (TB = n - 5 "lane bits", n = 5..10), so a warp carries
-// 32 / 2^TB samples and always 1024 amplitudes.  A *layout* says which logical wire sits on which
+// bits"); 2^TB threads share a sample (TB = n - 5 "thread bits", n = 5..13): for n <= 10 these are lanes of
+// one warp, which then carries 32 / 2^TB samples and always 1024 amplitudes; for n = 11..13 a sample spans
+// 2^(n-10) warps of one CTA (a "group"), which exchange through a group-wide shared buffer and a named barrier.  A *layout* says which logical wire sits on which
 // physical bit; gates act only on register bits, and an EXCHANGE micro-op re-lays the state out
 // through a warp-private shared-memory buffer with GF(2)-linear, bank-conflict-free addressing.
 // CNOTs cost nothing: they update the layout matrix and are materialised by the next exchange.
@@ -21,7 +22,8 @@ namespace vm {
 constexpr int kR = 5;                  // register bits
 constexpr int kAmps = 1 << kR;         // amplitudes per thread
 constexpr int kWarpAmps = 1024;        // amplitudes per warp (any TB)
-constexpr int kMinQubits = 5, kMaxQubits = 10;
+constexpr int kMinQubits = 5, kMaxQubits = 13;
+constexpr int kMaxThreadBits = kMaxQubits - kR;   // 8
 
 enum MopKind : int32_t {
   MOP_END = 0,
@@ -63,11 +65,13 @@ struct DiagDesc {      // per DIAG / DIAG_REG micro-op
   int32_t table;       // DIAG: offset (in float2) into the big-table area; DIAG_REG: into the small one
   int32_t is_reg;
   int32_t acc_reg[kR];   // accumulator index receiving sum_p z_bit(p) Im(conj(lam_p) psi_p), or -1
-  int32_t acc_lane[5];   // same for lane bits
+  int32_t acc_thr[kMaxThreadBits];   // same for thread bits (lane bits first, then warp bits)
 };
 
-struct Exchange {      // byte offsets into the warp's 8 KB buffer; address = base[lane] ^ off[j]
-  uint32_t wbase[32], woff[32], rbase[32], roff[32];
+struct Exchange {      // byte offsets into the group's buffer (8 KB per warp); address = base[thread] ^ off[j]
+  uint32_t woff[32], roff[32];
+  uint32_t base;       // first of 2 * G entries in Program::xbase (G = threads per group): write bases, then read bases
+  uint32_t pad[3];
 };
 
 struct GradSlot {      // gw[weight] += accumulator[acc]  (every gradient is a direct, already-reduced sum)
@@ -77,12 +81,14 @@ struct GradSlot {      // gw[weight] += accumulator[acc]  (every gradient is a d
 struct Program {
   bool ok = false;
   std::string why_not;           // when !ok: why the VM does not take this circuit (generic path used)
-  int n = 0, tb = 0;
+  int n = 0, tb = 0;             // tb = n - 5 thread bits
+  int wb = 0;                    // warp bits: max(0, n - 10); a group is 2^wb warps
   std::vector<MicroOp> ops;      // forward order, MOP_END-terminated
   std::vector<DevOp> coef_ops;   // recipes (gate kind + angle sources), one per 8-float coefficient row
   std::vector<DiagTerm> terms;
   std::vector<DiagDesc> diags;
   std::vector<Exchange> exchanges;
+  std::vector<uint32_t> xbase;   // per-thread base offsets of all exchanges
   std::vector<GradSlot> slots;
   int n_acc = 0;                 // floats of gradient accumulators
   int n_big_tables = 0, n_small_tables = 0;
@@ -94,6 +100,7 @@ struct Program {
   DiagTerm* d_terms = nullptr;
   DiagDesc* d_diags = nullptr;
   Exchange* d_exchanges = nullptr;
+  uint32_t* d_xbase = nullptr;
   GradSlot* d_slots = nullptr;
   int32_t* d_slot_ptr = nullptr;  // CSR weight -> slots
   int32_t* d_slot_idx = nullptr;
@@ -104,7 +111,7 @@ void compile(const qnn_circuit* c, Program* out);
 std::string describe(const Program& p);   // JSON, for tests and introspection
 
 struct Plan {
-  int threads, grid, warps_per_cta;
+  int threads, grid, warps_per_cta, fwd_threads;
   size_t smem_fwd, smem_bwd;
   size_t ws_coef, ws_diag, ws_partial;   // bytes (each 256-aligned)
 };

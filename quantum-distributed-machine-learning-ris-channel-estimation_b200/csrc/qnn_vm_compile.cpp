@@ -193,7 +193,7 @@ struct Builder {
     DiagDesc D{};
     D.first_term = (int)P->terms.size();
     for (int r = 0; r < kR; ++r) D.acc_reg[r] = -1;
-    for (int l = 0; l < 5; ++l) D.acc_lane[l] = -1;
+    for (int l = 0; l < kMaxThreadBits; ++l) D.acc_thr[l] = -1;
     bool reg_only = true;
     for (int i : pending) {
       const Item& it = items[i];
@@ -204,7 +204,7 @@ struct Builder {
       t.bit1 = it.kind == IT_CZ ? bit_of(it.w1) : -1;
       if (t.bit0 >= kR || t.bit1 >= kR) reg_only = false;
       if (t.kind == 0 && t.src >= 0) {
-        int32_t& a = t.bit0 < kR ? D.acc_reg[t.bit0] : D.acc_lane[t.bit0 - kR];
+        int32_t& a = t.bit0 < kR ? D.acc_reg[t.bit0] : D.acc_thr[t.bit0 - kR];
         if (a < 0) a = P->n_acc++;
         P->slots.push_back(GradSlot{t.src, a});
       }
@@ -276,7 +276,7 @@ struct Builder {
         m.a = bit_of(it.w1); m.acc = -1;
         const int cb = bit_of(it.w0);
         if (cb < kR) { m.kind = MOP_CU3_L; m.b = cb; }
-        else { m.kind = MOP_CU3_P; m.aux = 1 << (cb - kR); }
+        else { m.kind = MOP_CU3_P; m.aux = 1 << (cb - kR); }   // thread-bit mask (lanes, then warps)
         m.idx = new_coef_row(QNN_CU3, it.src, it.value, 3);
         bool any_w = false;
         for (int k = 0; k < 3; ++k) any_w |= it.src[k] >= 0;
@@ -314,20 +314,25 @@ struct Builder {
   bool emit_exchange(const int* new_bit_of_wire) {
     uint32_t inv_col[16];
     if (!invert(rowmask, n, inv_col)) { P->why_not = "internal: singular layout"; return false; }
+    // Extended index of an amplitude inside a group's buffer: bits 0..4 register index, 5..9 lane,
+    // 10.. warp-in-group.  For n < 10 the lanes above the sample's own are sample-in-warp bits and stay put.
+    const int E = 10 + P->wb;
     // acol[b']: old extended index contributed by new extended bit b'
-    uint32_t acol[10];
+    uint32_t acol[16];
     for (int w = 0; w < n; ++w) acol[new_bit_of_wire[w]] = inv_col[w];
-    for (int b = n; b < 10; ++b) acol[b] = 1u << b;      // sample-in-warp bits stay put
-    // slot map S (columns scol[e], 10-bit), bank-conflict-free for 64-bit accesses on both sides
+    for (int b = n; b < E; ++b) acol[b] = 1u << b;
+    // slot map S (columns scol[e], E bits), bank-conflict-free for 64-bit accesses on both sides:
+    // the low 4 slot bits must be a bijection of lane bits 0..3 (extended bits 5..8) for writer and reader
     Lcg rng{0x9E3779B97F4A7C15ULL + P->exchanges.size() * 7919ULL};
-    uint32_t scol[10], rcol[10];
+    uint32_t scol[16], rcol[16];
+    const uint32_t emask = (1u << E) - 1u;
     for (int attempt = 0;; ++attempt) {
-      if (attempt > 100000) { P->why_not = "internal: no conflict-free exchange found"; return false; }
-      for (int e = 0; e < 10; ++e) scol[e] = rng.next() & 1023u;
-      if (!independent(scol, 10)) continue;
-      for (int b = 0; b < 10; ++b) {
+      if (attempt > 200000) { P->why_not = "internal: no conflict-free exchange found"; return false; }
+      for (int e = 0; e < E; ++e) scol[e] = rng.next() & emask;
+      if (!independent(scol, E)) continue;
+      for (int b = 0; b < E; ++b) {
         uint32_t s = 0;
-        for (int e = 0; e < 10; ++e) if ((acol[b] >> e) & 1u) s ^= scol[e];
+        for (int e = 0; e < E; ++e) if ((acol[b] >> e) & 1u) s ^= scol[e];
         rcol[b] = s;
       }
       uint32_t wlow[4], rlow[4];
@@ -335,12 +340,19 @@ struct Builder {
       if (independent(wlow, 4) && independent(rlow, 4)) break;
     }
     Exchange X{};
+    const int G = 32 << P->wb;
+    X.base = (uint32_t)P->xbase.size();
     for (int v = 0; v < 32; ++v) {
-      uint32_t wb = 0, wo = 0, rb = 0, ro = 0;
-      for (int i = 0; i < 5; ++i) if ((v >> i) & 1) { wo ^= scol[i]; wb ^= scol[5 + i]; ro ^= rcol[i]; rb ^= rcol[5 + i]; }
-      X.wbase[v] = wb * 8; X.woff[v] = wo * 8;
-      X.rbase[v] = rb * 8; X.roff[v] = ro * 8;
+      uint32_t wo = 0, ro = 0;
+      for (int i = 0; i < 5; ++i) if ((v >> i) & 1) { wo ^= scol[i]; ro ^= rcol[i]; }
+      X.woff[v] = wo * 8; X.roff[v] = ro * 8;
     }
+    for (int side = 0; side < 2; ++side)
+      for (int t = 0; t < G; ++t) {
+        uint32_t b = 0;
+        for (int i = 0; i < 5 + P->wb; ++i) if ((t >> i) & 1) b ^= side ? rcol[5 + i] : scol[5 + i];
+        P->xbase.push_back(b * 8);
+      }
     MicroOp m{};
     m.kind = MOP_XCHG; m.idx = (int)P->exchanges.size(); m.acc = -1;
     P->exchanges.push_back(X);
@@ -432,8 +444,8 @@ struct Builder {
   bool run() {
     n = c->n_qubits;
     tb = n - kR;
-    P->n = n; P->tb = tb;
-    if (n < kMinQubits || n > kMaxQubits) { P->why_not = "n_qubits outside [5, 10]"; return false; }
+    P->n = n; P->tb = tb; P->wb = n > 10 ? n - 10 : 0;
+    if (n < kMinQubits || n > kMaxQubits) { P->why_not = "n_qubits outside [5, 13]"; return false; }
     if (c->encoder != QNN_ENC_NONE) { P->why_not = "amplitude encoder"; return false; }
     if (c->n_inputs > 32) { P->why_not = "more than 32 input columns"; return false; }
     if (!lower_items()) return false;
@@ -556,7 +568,7 @@ std::string describe(const Program& p) {
   o.precision(9);
   o << "{\"ok\": " << (p.ok ? "true" : "false") << ", \"why_not\": \"" << p.why_not << "\"";
   if (!p.ok) { o << "}"; return o.str(); }
-  o << ", \"n\": " << p.n << ", \"tb\": " << p.tb << ", \"n_acc\": " << p.n_acc;
+  o << ", \"n\": " << p.n << ", \"tb\": " << p.tb << ", \"wb\": " << p.wb << ", \"n_acc\": " << p.n_acc;
   auto arr = [&](const char* name, const int* v, int cnt) {
     o << ", \"" << name << "\": [";
     for (int i = 0; i < cnt; ++i) o << (i ? ", " : "") << v[i];
@@ -585,21 +597,24 @@ std::string describe(const Program& p) {
     }
     o << "], \"acc_reg\": [";
     for (int r = 0; r < kR; ++r) o << (r ? ", " : "") << D.acc_reg[r];
-    o << "], \"acc_lane\": [";
-    for (int r = 0; r < 5; ++r) o << (r ? ", " : "") << D.acc_lane[r];
+    o << "], \"acc_thr\": [";
+    for (int r = 0; r < kMaxThreadBits; ++r) o << (r ? ", " : "") << D.acc_thr[r];
     o << "]}";
   }
   o << "], \"exchanges\": [";
+  const int G = 32 << p.wb;
   for (size_t i = 0; i < p.exchanges.size(); ++i) {
     const Exchange& X = p.exchanges[i];
     o << (i ? ", " : "") << "{";
-    const uint32_t* tabs[4] = {X.wbase, X.woff, X.rbase, X.roff};
-    const char* names[4] = {"wbase", "woff", "rbase", "roff"};
-    for (int t = 0; t < 4; ++t) {
-      o << (t ? ", " : "") << "\"" << names[t] << "\": [";
-      for (int v = 0; v < 32; ++v) o << (v ? ", " : "") << tabs[t][v];
+    auto tab = [&](const char* name, const uint32_t* v, int cnt, bool first) {
+      o << (first ? "" : ", ") << "\"" << name << "\": [";
+      for (int k = 0; k < cnt; ++k) o << (k ? ", " : "") << v[k];
       o << "]";
-    }
+    };
+    tab("wbase", p.xbase.data() + X.base, G, true);
+    tab("woff", X.woff, 32, false);
+    tab("rbase", p.xbase.data() + X.base + G, G, false);
+    tab("roff", X.roff, 32, false);
     o << "}";
   }
   o << "], \"slots\": [";

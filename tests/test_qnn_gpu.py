@@ -175,7 +175,8 @@ def test_kernel_family_selection_and_both_families_agree(monkeypatch):
             assert_close(u, v, rel=2e-5, scale=float(np.abs(v).max()), what=name)
         check_against_oracle(slow, 33, seed=1)
     assert _plan(qris_b200.reference_circuit(4, 1), 8).startswith("generic")
-    assert _plan(qris_b200.reference_circuit(12, 1), 8).startswith("generic")
+    assert _plan(qris_b200.reference_circuit(12, 1), 8) == "vm-register"
+    assert _plan(qris_b200.reference_circuit(14, 1), 8).startswith("generic")
 
 
 @pytest.mark.parametrize("n", [5, 6, 7, 8, 9, 10])
@@ -184,6 +185,15 @@ def test_vm_all_widths_and_ragged_batches(n, B):
     """Every lane/sample geometry of the VM (2^(n-5) lanes per sample), including partially filled warps."""
     check_against_oracle(qris_b200.reference_circuit(n, 2), B, seed=n * 7 + B)
     check_against_oracle(qris_b200.u3cu3_circuit(n, 1), B, seed=n * 11 + B)
+
+
+@pytest.mark.parametrize("n", [11, 12, 13])
+@pytest.mark.parametrize("B", [1, 5, 40])
+def test_vm_multi_warp_samples(n, B):
+    """n = 11..13 on the VM: one sample per 2^(n-10) warps, group-wide exchanges and cross-warp sums."""
+    assert _plan(qris_b200.u3cu3_circuit(n, 1), B) == "vm-register"
+    check_against_oracle(qris_b200.u3cu3_circuit(n, 1), B, seed=n + B)
+    check_against_oracle(qris_b200.reference_circuit(n, 2), B, seed=n * 3 + B)
 
 
 def test_vm_irregular_circuit():

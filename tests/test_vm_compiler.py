@@ -13,7 +13,7 @@ from vm_emulator import emulate_forward
 def _check(circ, seed=0):
     desc = circ.describe()
     assert desc["ok"], desc["why_not"]
-    spw = 32 >> desc["tb"]
+    spw = (32 >> desc["tb"]) if desc.get("wb", 0) == 0 else 1
     rng = np.random.default_rng(seed)
     x = rng.uniform(-1, 1, (spw, circ.n_inputs))
     w = rng.uniform(0, 2 * np.pi, circ.n_weights)
@@ -39,6 +39,14 @@ def test_u3cu3_program(n, L):
         assert stats["xchg"] <= 3 * L and stats["cg_p"] <= 2 * L
 
 
+@pytest.mark.parametrize("n,L", [(11, 1), (12, 2), (13, 1)])
+def test_multi_warp_samples(n, L):
+    """n = 11..13: a sample spans 2^(n-10) warps; exchanges address a group-wide buffer."""
+    desc, stats = _check(qris_b200.reference_circuit(n, L), seed=n)
+    assert desc["wb"] == n - 10 and len(desc["exchanges"][0]["wbase"]) == 32 << (n - 10)
+    _check(qris_b200.u3cu3_circuit(n, 1), seed=n + 1)
+
+
 def test_irregular_program():
     Op = qris_b200.Op
     n = 7
@@ -54,4 +62,4 @@ def test_out_of_scope_circuits_report_why():
     assert not qris_b200.reference_circuit(4, 1).describe()["ok"]
     d = qris_b200.u3cu3_circuit(6, 1, encoder="amplitude").describe()
     assert not d["ok"] and "amplitude" in d["why_not"]
-    assert not qris_b200.reference_circuit(12, 1).describe()["ok"]
+    assert not qris_b200.reference_circuit(14, 1).describe()["ok"]

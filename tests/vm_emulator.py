@@ -35,7 +35,7 @@ def _apply_reg(state, U, rbit, lane_mask=None, ctrl_rbit=None):
     if ctrl_rbit is not None:
         j0 = j0[(j0 >> ctrl_rbit) & 1 == 1]
     j1 = j0 | (1 << rbit)
-    lanes = np.arange(32) if lane_mask is None else np.nonzero(lane_mask)[0]
+    lanes = np.arange(state.shape[0]) if lane_mask is None else np.nonzero(lane_mask)[0]
     a0 = state[np.ix_(lanes, j0)].copy()
     a1 = state[np.ix_(lanes, j1)].copy()
     state[np.ix_(lanes, j0)] = U[0, 0] * a0 + U[0, 1] * a1
@@ -44,7 +44,7 @@ def _apply_reg(state, U, rbit, lane_mask=None, ctrl_rbit=None):
 
 def check_conflict_free(base, off):
     for j in range(32):
-        for half in (0, 16):
+        for half in range(0, len(base), 16):          # every half-warp of every warp of the group
             slots = {((base[l] ^ off[j]) // 8) % 16 for l in range(half, half + 16)}
             assert len(slots) == 16, "shared-memory bank conflict in an exchange"
 
@@ -52,15 +52,16 @@ def check_conflict_free(base, off):
 def emulate_forward(desc, x, w):
     """x: (samples_per_warp, n_inputs); returns y (samples_per_warp, n)."""
     assert desc["ok"]
-    n, tb = desc["n"], desc["tb"]
-    T = 1 << tb
-    spw = 32 // T
+    n, tb, wb = desc["n"], desc["tb"], desc.get("wb", 0)
+    G = 32 << wb                          # threads per group (one warp for n <= 10)
+    T = 1 << tb                           # threads per sample
+    spw = G // T if wb == 0 else 1
     assert x.shape[0] == spw
-    state = np.zeros((32, 32), complex)
+    state = np.zeros((G, 32), complex)
     for s in range(spw):
         state[s * T, 0] = 1.0
-    lane = np.arange(32)
-    lis = lane % T                       # lane in sample
+    lane = np.arange(G)
+    lis = lane % T                       # thread in sample
     samp = lane // T
     stats = {"xchg": 0, "diag": 0, "diag_reg": 0, "g1": 0, "cg_l": 0, "cg_p": 0}
     for kind, a, b, idx, acc, aux in desc["ops"]:
@@ -107,7 +108,7 @@ def emulate_forward(desc, x, w):
             assert bool(D["is_reg"]) == (kind == MOP_DIAG_REG)
             j = np.arange(32)
             p = j[None, :] | (lis[:, None] << 5)         # physical index of (lane, j) within its sample
-            ang = np.zeros((32, 32))
+            ang = np.zeros((G, 32))
             for tkind, src, value, bit0, bit1 in D["terms"]:
                 if tkind == 0:
                     z = 1 - 2 * ((p >> bit0) & 1)
@@ -123,13 +124,13 @@ def emulate_forward(desc, x, w):
             check_conflict_free(X["wbase"], X["woff"])
             check_conflict_free(X["rbase"], X["roff"])
             buf = {}
-            for l in range(32):
+            for l in range(G):
                 for jj in range(32):
                     addr = X["wbase"][l] ^ X["woff"][jj]
-                    assert addr % 8 == 0 and 0 <= addr < 8192 and addr not in buf
+                    assert addr % 8 == 0 and 0 <= addr < 8192 * (G // 32) and addr not in buf
                     buf[addr] = state[l, jj]
             new = np.empty_like(state)
-            for l in range(32):
+            for l in range(G):
                 for jj in range(32):
                     new[l, jj] = buf[X["rbase"][l] ^ X["roff"][jj]]
             state = new
