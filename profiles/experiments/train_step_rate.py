@@ -1,0 +1,23 @@
+"""Experiment: optimiser steps per second of the reference's as-shipped training configuration
+(n = 6, L = 3, nine user batches of 256; Runner_P128...py:20-34) through runner.qsc_step."""
+import sys, os, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+import torch
+from qris_b200 import estimators as E, optim, runner
+r = runner.Y2HRunner(data_len=2560, batch_size_DML=256, device="cuda", verbose=False)
+loader, _ = r.get_dataloader_DML()
+batches = list(loader)
+for concat in (False, True):
+    torch.manual_seed(0)
+    model = E.QSC_P128(use_quantumnat=False, use_gradient_pruning=False).cuda().train()
+    opt = optim.FlatPrunedAdamW(model.parameters(), lr=1e-3, weight_decay=0.01)
+    for b in batches[:3]:
+        r.qsc_step(model, opt, b, concat)
+    torch.cuda.synchronize(); t0 = time.perf_counter()
+    n = 0
+    for rep in range(5):
+        for b in batches:
+            r.qsc_step(model, opt, b, concat); n += 1
+    torch.cuda.synchronize(); dt = time.perf_counter() - t0
+    print(f"concat_users={concat}: {n / dt:.1f} optimiser steps/s = {n * 9 * 256 / dt / 1e3:.1f} k circuit-samples/s "
+          f"(fwd+bwd+optimiser, whole QSC model); one reference epoch (71 steps) = {71 * dt / n:.2f} s")

@@ -36,7 +36,6 @@ struct VmArgs {
   int n, tb, wb, n_inputs, n_acc;           // tb = n - 5 thread bits; wb = warp bits (a group = 2^wb warps)
   const uint32_t* xbase; int n_xbase;       // per-thread exchange bases
   unsigned table_bytes;                     // shared-memory bytes of all tables (to place them around the buffers)
-  unsigned skip_mask;                       // experiments only (QNN_VM_SKIP): micro-op kinds to skip
   int8_t wire_of_bit[16];                   // final (measurement) layout
   const float* x; float* y;                 // forward
   const float* gy; float* gx; float* partial;  // backward; partial [grid][n_acc]
@@ -183,32 +182,6 @@ __device__ __forceinline__ void cu3_all_bwd(float2 (&ps)[NA], float2 (&ls)[NA], 
     cu3_pair_bwd(g, ps[j0], ps[j1], ls[j0], ls[j1], A);
   }
 }
-
-#define RB_SWITCH(rb, CALL)          \
-  switch (rb) {                      \
-    case 0: { CALL(0); } break;      \
-    case 1: { CALL(1); } break;      \
-    case 2: { CALL(2); } break;      \
-    case 3: { CALL(3); } break;      \
-    default: { CALL(4); } break;     \
-  }
-// (target, control) pairs, control != target
-#define RC_CASES(RT, CALL)                                 \
-  switch (rc) {                                            \
-    case 0: if constexpr (RT != 0) { CALL(RT, 0); } break; \
-    case 1: if constexpr (RT != 1) { CALL(RT, 1); } break; \
-    case 2: if constexpr (RT != 2) { CALL(RT, 2); } break; \
-    case 3: if constexpr (RT != 3) { CALL(RT, 3); } break; \
-    default: if constexpr (RT != 4) { CALL(RT, 4); } break; \
-  }
-#define RTC_SWITCH(rt, CALL)               \
-  switch (rt) {                            \
-    case 0: RC_CASES(0, CALL) break;       \
-    case 1: RC_CASES(1, CALL) break;       \
-    case 2: RC_CASES(2, CALL) break;       \
-    case 3: RC_CASES(3, CALL) break;       \
-    default: RC_CASES(4, CALL) break;      \
-  }
 
 // ---- sums over the 32 register amplitudes: total and, per register bit r, the signed sum -------------
 // S[r] = sum_j (-1)^{j_r} v_j with a shared tree (61 packed adds); v_j are pairs, reduced per half.
@@ -484,7 +457,6 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
       for (int pc = 0; op.pad0 != H_END; ++pc) {
         const MicroOp next = S.ops[pc + 1];
         const float4 ncfa = *reinterpret_cast<const float4*>(S.coef + next.pad1 * 8);
-        if ((a.skip_mask >> op.kind) & 1u) { op = next; cfa = ncfa; continue; }
         switch (op.pad0) {
 #define H_CASE_ROT(RB) case H_ROT + RB: rot<RB>(ps, cfa.x, cfa.y); break;
           H_CASE_ROT(0) H_CASE_ROT(1) H_CASE_ROT(2) H_CASE_ROT(3) H_CASE_ROT(4)
@@ -607,7 +579,6 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
       for (int pc = a.n_ops - 2; pc >= 0; --pc) {
         const MicroOp next = S.ops[pc > 0 ? pc - 1 : 0];
         const float4 ncfa = *reinterpret_cast<const float4*>(S.coef + next.pad1 * 8);
-        if ((a.skip_mask >> op.kind) & 1u) { op = next; cfa = ncfa; continue; }
         switch (op.pad0) {
 #define H_CASE_ROT(RB) case H_ROT + RB: { float v = rot_grad<RB>(ps, ls); rot<RB>(ps, -cfa.x, -cfa.y); rot<RB>(ls, -cfa.x, -cfa.y); \
             if (op.acc >= 0) { v = warp_sum(v); if (lane == 0) wacc[op.acc] += v; } } break;
@@ -838,7 +809,6 @@ void fill_args(const qnn_circuit* c, const Program& p, const Plan& pl, void* ws,
   a->small = a->big + (size_t)p.n_big_tables * 32 * G; a->n_small = p.n_small_tables;
   a->n = p.n; a->tb = p.tb; a->wb = p.wb; a->n_inputs = c->n_inputs; a->n_acc = p.n_acc;
   a->table_bytes = (unsigned)table_bytes(p, c->n_inputs, (bwd ? kBwdThreads : kFwdThreads) / 32, bwd);
-  { const char* e = getenv("QNN_VM_SKIP"); a->skip_mask = e ? (unsigned)strtoul(e, nullptr, 0) : 0u; }
   for (int b = 0; b < 16; ++b) a->wire_of_bit[b] = 0;
   for (int w = 0; w < p.n; ++w) a->wire_of_bit[p.final_bit_of_wire[w]] = (int8_t)w;
   a->partial = reinterpret_cast<float*>(wsb + pl.ws_coef + pl.ws_diag);
