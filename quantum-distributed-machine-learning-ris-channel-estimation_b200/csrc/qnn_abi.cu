@@ -198,7 +198,7 @@ extern "C" int32_t qnn_backward_launches(const qnn_circuit* c, int64_t B) {
 extern "C" size_t qnn_forward_workspace_bytes(const qnn_circuit* c, int64_t B) {
   if (!c || B <= 0) return 0;
   vm::Plan vp;
-  if (vm_plan(c, B, &vp)) return vp.ws_coef + vp.ws_diag;
+  if (vm_plan(c, B, &vp)) return vp.ws_coef + vp.ws_diag + vp.ws_partial + vp.ws_cluster;
   GenericPlan p;
   generic_plan(c, B, &p);
   return p.ws_coef + p.ws_state_fwd;
@@ -206,7 +206,7 @@ extern "C" size_t qnn_forward_workspace_bytes(const qnn_circuit* c, int64_t B) {
 extern "C" size_t qnn_backward_workspace_bytes(const qnn_circuit* c, int64_t B) {
   if (!c || B <= 0) return 0;
   vm::Plan vp;
-  if (vm_plan(c, B, &vp)) return vp.ws_coef + vp.ws_diag + vp.ws_partial;
+  if (vm_plan(c, B, &vp)) return vp.ws_coef + vp.ws_diag + vp.ws_partial + vp.ws_cluster;
   GenericPlan p;
   generic_plan(c, B, &p);
   return p.ws_coef + p.ws_state_bwd + p.ws_partial;

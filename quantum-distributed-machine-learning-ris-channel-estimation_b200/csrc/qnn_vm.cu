@@ -36,6 +36,9 @@ struct VmArgs {
   int n, tb, wb, n_inputs, n_acc;           // tb = n - 5 thread bits; wb = warp bits (a group = 2^wb warps)
   const uint32_t* xbase; int n_xbase;       // per-thread exchange bases
   unsigned table_bytes;                     // shared-memory bytes of all tables (to place them around the buffers)
+  int cluster;                              // CTAs per sample (cluster geometry), else 0
+  unsigned char* cbuf;                      // cluster geometry: [clusters][2^n * 8] exchange buffers (workspace)
+  float* cred;                              // cluster geometry: [clusters][group warps][48] cross-CTA partials
   int8_t wire_of_bit[16];                   // final (measurement) layout
   const float* x; float* y;                 // forward
   const float* gy; float* gx; float* partial;  // backward; partial [grid][n_acc]
@@ -49,6 +52,14 @@ __device__ __forceinline__ void sts64(uint32_t addr, float a, float b) {
 }
 __device__ __forceinline__ void lds64(uint32_t addr, float& a, float& b) {
   asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(a), "=f"(b) : "r"(addr) : "memory");
+}
+
+__device__ __forceinline__ void stg64(unsigned char* base, uint32_t off, float a, float b) {
+  __stcg(reinterpret_cast<float2*>(base + off), make_float2(a, b));
+}
+__device__ __forceinline__ void ldg64(const unsigned char* base, uint32_t off, float& a, float& b) {
+  const float2 v = __ldcg(reinterpret_cast<const float2*>(base + off));
+  a = v.x; b = v.y;
 }
 
 template <int RB>
@@ -287,6 +298,44 @@ __device__ __forceinline__ void exchange(float2 (&st)[NA], uint32_t wa, uint32_t
   }
 }
 
+// Cluster geometry (n >= 14): the buffers are slices of the workspace (L2), accessed around L1.  Buffer
+// sets alternate from one exchange to the next, so ONE cluster barrier per exchange suffices: a set is
+// written again only after every thread has passed the barrier of the exchange in between, i.e. after
+// all reads of it have completed.  TWO: psi and lam travel together (backward), sharing that barrier.
+template <bool TWO, typename Sync>
+__device__ __forceinline__ void exchange_global(float2 (&st)[NA], float2 (&st2)[NA], unsigned char* buf, unsigned char* buf2,
+                                                uint32_t wa, uint32_t ra, const uint32_t* woff, const uint32_t* roff, Sync sync) {
+#pragma unroll
+  for (int q = 0; q < NA / 4; ++q) {
+    const uint4 o = *reinterpret_cast<const uint4*>(woff + 4 * q);
+    stg64(buf, wa ^ o.x, st[4 * q + 0].x, st[4 * q + 0].y);
+    stg64(buf, wa ^ o.y, st[4 * q + 1].x, st[4 * q + 1].y);
+    stg64(buf, wa ^ o.z, st[4 * q + 2].x, st[4 * q + 2].y);
+    stg64(buf, wa ^ o.w, st[4 * q + 3].x, st[4 * q + 3].y);
+    if (TWO) {
+      stg64(buf2, wa ^ o.x, st2[4 * q + 0].x, st2[4 * q + 0].y);
+      stg64(buf2, wa ^ o.y, st2[4 * q + 1].x, st2[4 * q + 1].y);
+      stg64(buf2, wa ^ o.z, st2[4 * q + 2].x, st2[4 * q + 2].y);
+      stg64(buf2, wa ^ o.w, st2[4 * q + 3].x, st2[4 * q + 3].y);
+    }
+  }
+  sync();
+#pragma unroll
+  for (int q = 0; q < NA / 4; ++q) {
+    const uint4 o = *reinterpret_cast<const uint4*>(roff + 4 * q);
+    ldg64(buf, ra ^ o.x, st[4 * q + 0].x, st[4 * q + 0].y);
+    ldg64(buf, ra ^ o.y, st[4 * q + 1].x, st[4 * q + 1].y);
+    ldg64(buf, ra ^ o.z, st[4 * q + 2].x, st[4 * q + 2].y);
+    ldg64(buf, ra ^ o.w, st[4 * q + 3].x, st[4 * q + 3].y);
+    if (TWO) {
+      ldg64(buf2, ra ^ o.x, st2[4 * q + 0].x, st2[4 * q + 0].y);
+      ldg64(buf2, ra ^ o.y, st2[4 * q + 1].x, st2[4 * q + 1].y);
+      ldg64(buf2, ra ^ o.z, st2[4 * q + 2].x, st2[4 * q + 2].y);
+      ldg64(buf2, ra ^ o.w, st2[4 * q + 3].x, st2[4 * q + 3].y);
+    }
+  }
+}
+
 // multiply by a diagonal (optionally its conjugate): big table [j][lane] or register-only table [j].
 // d*a = d.re * a + (-d.im, d.im) (.) swap(a); one table load serves psi and lam in the backward pass.
 template <bool CONJ, bool TWO>
@@ -325,13 +374,13 @@ struct Smem {
   uint32_t xbuf;      // shared address of this group's exchange buffer (8 KB per warp, aligned to its size)
 };
 
-size_t table_bytes(const Program& p, int n_inputs, int warps, bool bwd) {
+size_t table_bytes(const Program& p, int n_inputs, int warps, bool bwd, bool cluster) {
   auto up = [](size_t v) { return (v + 15) & ~size_t(15); };
   const int G = 32 << p.wb, spw = p.wb ? 1 : (32 >> p.tb);
   size_t b = 0;
   b += up(p.ops.size() * sizeof(MicroOp));
   b += up(p.exchanges.size() * sizeof(Exchange));
-  b += up(p.xbase.size() * sizeof(uint32_t));
+  if (!cluster) b += up(p.xbase.size() * sizeof(uint32_t));
   b += up(p.diags.size() * sizeof(DiagDesc));
   b += up(p.coef_ops.size() * 8 * sizeof(float));
   if (p.wb == 0) b += up((size_t)p.n_big_tables * 32 * G * sizeof(float2));
@@ -344,22 +393,33 @@ size_t table_bytes(const Program& p, int n_inputs, int warps, bool bwd) {
   }
   return b;
 }
-// exchange buffers (8 KB per warp, each group's aligned to its size) + worst-case alignment gap + tables
-size_t smem_bytes(const Program& p, int n_inputs, int warps, bool bwd) {
+// exchange buffers (8 KB per warp, each group's aligned to its size) + worst-case alignment gap + tables;
+// the cluster geometry keeps its exchange buffer in the workspace
+size_t smem_bytes(const Program& p, int n_inputs, int warps, bool bwd, bool cluster) {
+  if (cluster) return table_bytes(p, n_inputs, warps, bwd, true) + 64;
   const size_t group_buf = (size_t)8192 << p.wb;
-  return group_buf + (size_t)warps * 8192 + table_bytes(p, n_inputs, warps, bwd) + 64;
+  return group_buf + (size_t)warps * 8192 + table_bytes(p, n_inputs, warps, bwd, false) + 64;
 }
 
-// MW: a sample spans several warps (n > 10).  MW = false compiles the single-warp geometry with constant
-// strides and __syncwarp barriers.
-template <bool BWD, int THREADS, int MINB, bool STATE, bool MW>
+// GEOM 0: a warp carries whole samples (n <= 10): constant strides, __syncwarp barriers.
+// GEOM 1: a sample spans 2^wb warps of one CTA (n = 11..13): shared exchange buffer, named barriers.
+// GEOM 2: a sample spans a thread-block cluster (n = 14..16): exchange buffer in L2, cluster barriers,
+//         per-thread bases and cross-CTA partial sums in global memory.
+template <bool BWD, int THREADS, int MINB, bool STATE, int GEOM>
 __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  constexpr int WARPS = THREADS / 32;
+  const int WARPS = blockDim.x >> 5;     // THREADS is the launch bound; fewer warps may be launched
+  constexpr bool MW = GEOM >= 1, CL = GEOM == 2;
   const int tb = a.tb, wbits = MW ? a.wb : 0;
   const int gwarps = 1 << wbits, G = 32 << wbits;          // warps / threads per group (one sample for n >= 10)
-  const int gw = warp & (gwarps - 1), grp = warp >> wbits, groups = WARPS >> wbits;
+  unsigned crank = 0, cid = blockIdx.x, ncl = gridDim.x;   // cluster rank / id / count (GEOM 2)
+  if constexpr (CL) {
+    asm("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
+    cid = blockIdx.x / (unsigned)a.cluster; ncl = gridDim.x / (unsigned)a.cluster;
+  }
+  const int gw = CL ? (int)crank * WARPS + warp : (warp & (gwarps - 1));   // warp in group
+  const int grp = CL ? 0 : (warp >> wbits), groups = CL ? 1 : (WARPS >> wbits);
   const int spw = wbits ? 1 : (32 >> tb);                  // samples per warp (n <= 10)
   const int tig = (gw << 5) | lane;                        // thread in group
   const int tis = wbits ? tig : (lane & ((1 << tb) - 1));  // thread in sample: the sample's thread bits
@@ -371,15 +431,15 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
   Smem S;
   {
     const uint32_t s0 = (uint32_t)__cvta_generic_to_shared(smem_raw);
-    const uint32_t gbuf = 8192u << wbits;
+    const uint32_t gbuf = CL ? 16u : (8192u << wbits);
     const uint32_t xb = (s0 + gbuf - 1u) & ~(gbuf - 1u);
     S.xbuf = xb + (uint32_t)grp * gbuf;
     const size_t tables = a.table_bytes;
-    unsigned char* p = (xb - s0 >= tables) ? smem_raw : smem_raw + (xb - s0) + (size_t)WARPS * 8192;
+    unsigned char* p = CL ? smem_raw : ((xb - s0 >= tables) ? smem_raw : smem_raw + (xb - s0) + (size_t)WARPS * 8192);
     auto take = [&](size_t bytes) { unsigned char* r = p; p += (bytes + 15) & ~size_t(15); return r; };
     S.ops = reinterpret_cast<MicroOp*>(take((size_t)a.n_ops * sizeof(MicroOp)));
     S.exchanges = reinterpret_cast<Exchange*>(take((size_t)a.n_exchanges * sizeof(Exchange)));
-    S.xbase = reinterpret_cast<uint32_t*>(take((size_t)a.n_xbase * sizeof(uint32_t)));
+    S.xbase = CL ? const_cast<uint32_t*>(a.xbase) : reinterpret_cast<uint32_t*>(take((size_t)a.n_xbase * sizeof(uint32_t)));
     S.diags = reinterpret_cast<DiagDesc*>(take((size_t)a.n_diags * sizeof(DiagDesc)));
     S.coef = reinterpret_cast<float*>(take((size_t)a.n_coef * 8 * sizeof(float)));
     float2* sbig = wbits == 0 ? reinterpret_cast<float2*>(take((size_t)a.n_big * 32 * G * sizeof(float2))) : nullptr;
@@ -394,18 +454,18 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
     const int tid = threadIdx.x;
     const uint32_t* src; uint32_t* dst; int words;
     src = reinterpret_cast<const uint32_t*>(a.ops); dst = reinterpret_cast<uint32_t*>(S.ops); words = a.n_ops * (int)(sizeof(MicroOp) / 4);
-    for (int i = tid; i < words; i += THREADS) dst[i] = src[i];
+    for (int i = tid; i < words; i += blockDim.x) dst[i] = src[i];
     src = reinterpret_cast<const uint32_t*>(a.exchanges); dst = reinterpret_cast<uint32_t*>(S.exchanges); words = a.n_exchanges * (int)(sizeof(Exchange) / 4);
-    for (int i = tid; i < words; i += THREADS) dst[i] = src[i];
-    for (int i = tid; i < a.n_xbase; i += THREADS) S.xbase[i] = a.xbase[i];
+    for (int i = tid; i < words; i += blockDim.x) dst[i] = src[i];
+    if (!CL) for (int i = tid; i < a.n_xbase; i += blockDim.x) S.xbase[i] = a.xbase[i];
     src = reinterpret_cast<const uint32_t*>(a.diags); dst = reinterpret_cast<uint32_t*>(S.diags); words = a.n_diags * (int)(sizeof(DiagDesc) / 4);
-    for (int i = tid; i < words; i += THREADS) dst[i] = src[i];
-    for (int i = tid; i < a.n_coef * 8; i += THREADS) S.coef[i] = a.coef[(size_t)(i >> 3) * QNN_COEF_STRIDE + (i & 7)];
-    if (wbits == 0) for (int i = tid; i < a.n_big * 32 * G; i += THREADS) sbig[i] = a.big[i];
-    for (int i = tid; i < a.n_small * 32; i += THREADS) S.small[i] = a.small[i];
+    for (int i = tid; i < words; i += blockDim.x) dst[i] = src[i];
+    for (int i = tid; i < a.n_coef * 8; i += blockDim.x) S.coef[i] = a.coef[(size_t)(i >> 3) * QNN_COEF_STRIDE + (i & 7)];
+    if (wbits == 0) for (int i = tid; i < a.n_big * 32 * G; i += blockDim.x) sbig[i] = a.big[i];
+    for (int i = tid; i < a.n_small * 32; i += blockDim.x) S.small[i] = a.small[i];
     if (BWD) {
-      for (int i = tid; i < WARPS * max(a.n_acc, 1); i += THREADS) S.wacc[i] = 0.f;
-      for (int i = tid; i < WARPS * spw * max(a.n_inputs, 1); i += THREADS) S.gxacc[i] = 0.f;
+      for (int i = tid; i < WARPS * max(a.n_acc, 1); i += blockDim.x) S.wacc[i] = 0.f;
+      for (int i = tid; i < WARPS * spw * max(a.n_inputs, 1); i += blockDim.x) S.gxacc[i] = 0.f;
     }
   }
   __syncthreads();
@@ -415,13 +475,22 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
   // barrier over the threads that share one exchange buffer
   auto gsync = [&]() {
     if constexpr (!MW) __syncwarp();
-    else asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "r"(G) : "memory");
+    else if constexpr (!CL) asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "r"(G) : "memory");
+    else {   // every thread of every CTA of the cluster; release/acquire orders the global exchange traffic
+      asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    }
   };
+  // cluster geometry: four exchange buffers per cluster (two alternating sets of {psi, lam})
+  unsigned char* const cbuf = CL ? a.cbuf + ((size_t)cid << (a.n + 5)) : nullptr;
+  const size_t cbuf_one = (size_t)1 << (a.n + 3);
+  unsigned xpar = 0;
+  float* const cred = CL ? a.cred + (size_t)cid * gwarps * 48 : nullptr;
 
   float2* const xcoef = S.xcoef + (size_t)warp * spw * max(a.n_inputs, 1);
   float2 ps[NA];
   const long long n_batches = (a.B + spw - 1) / spw;
-  for (long long wb = (long long)blockIdx.x * groups + grp; wb < n_batches; wb += (long long)gridDim.x * groups) {
+  for (long long wb = CL ? (long long)cid : (long long)blockIdx.x * groups + grp; wb < n_batches;
+       wb += CL ? (long long)ncl : (long long)gridDim.x * groups) {
     const long long bs = wb * spw + siw;
     const bool active = bs < a.B;
     gsync();   // nothing of the previous batch (scratch, exchange buffer) is still being read
@@ -498,7 +567,11 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
           case H_DIAGR: diag_mul<false, false>(ps, ps, S.small + op.idx * 32, 1, 0); break;
           case H_XCHG: {
             const Exchange* X = S.exchanges + op.idx;
-            exchange(ps, S.xbuf | S.xbase[X->base + tig], S.xbuf | S.xbase[X->base + G + tig], X->woff, X->roff, gsync);
+            if constexpr (CL) {
+              xpar ^= 1u;
+              unsigned char* b0 = cbuf + (size_t)(2 * xpar) * cbuf_one;
+              exchange_global<false>(ps, ps, b0, b0, S.xbase[X->base + tig], S.xbase[X->base + G + tig], X->woff, X->roff, gsync);
+            } else exchange(ps, S.xbuf | S.xbase[X->base + tig], S.xbuf | S.xbase[X->base + G + tig], X->woff, X->roff, gsync);
           } break;
           default: break;
         }
@@ -534,19 +607,21 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
             if (pb < a.n) yrow[a.wire_of_bit[pb]] = val[pb];
         }
       } else {
-        // a sample spans 2^wb warps: combine their partials through shared memory (fixed order)
+        // a sample spans 2^wb warps: combine their partials through shared (or, for a cluster, global)
+        // memory in a fixed order
+        float* const mine = CL ? cred + (size_t)gw * 48 : red;
         if (lane == 0) {
 #pragma unroll
-          for (int c = 0; c < 11; ++c) red[c] = val[c];
+          for (int c = 0; c < 11; ++c) { if (CL) __stcg(mine + c, val[c]); else mine[c] = val[c]; }
         }
         gsync();
         if (gw == 0 && lane < a.n && active) {
-          const float* r0 = S.red + (size_t)(grp << wbits) * 16;
+          const float* r0 = CL ? cred : S.red + (size_t)(grp << wbits) * 16;
+          const int stride = CL ? 48 : 16;
           float t = 0.f;
-          if (lane < 10) {
-            for (int w = 0; w < gwarps; ++w) t += r0[w * 16 + lane];
-          } else {
-            for (int w = 0; w < gwarps; ++w) t += ((w >> (lane - 10)) & 1) ? -r0[w * 16 + 10] : r0[w * 16 + 10];
+          for (int w = 0; w < gwarps; ++w) {
+            const float v = CL ? __ldcg(r0 + w * stride + (lane < 10 ? lane : 10)) : r0[w * stride + (lane < 10 ? lane : 10)];
+            t += (lane >= 10 && ((w >> (lane - 10)) & 1)) ? -v : v;
           }
           a.y[(size_t)bs * a.n + a.wire_of_bit[lane]] = t;
         }
@@ -679,9 +754,16 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
           } break;
           case H_XCHG: {   // inverse: roles of the two address sets swapped
             const Exchange* X = S.exchanges + op.idx;
-            const uint32_t wa = S.xbuf | S.xbase[X->base + G + tig], ra = S.xbuf | S.xbase[X->base + tig];
-            exchange(ps, wa, ra, X->roff, X->woff, gsync);
-            exchange(ls, wa, ra, X->roff, X->woff, gsync);
+            if constexpr (CL) {
+              const uint32_t wa = S.xbase[X->base + G + tig], ra = S.xbase[X->base + tig];
+              xpar ^= 1u;
+              unsigned char* b0 = cbuf + (size_t)(2 * xpar) * cbuf_one;
+              exchange_global<true>(ps, ls, b0, b0 + cbuf_one, wa, ra, X->roff, X->woff, gsync);
+            } else {
+              const uint32_t wa = S.xbuf | S.xbase[X->base + G + tig], ra = S.xbuf | S.xbase[X->base + tig];
+              exchange(ps, wa, ra, X->roff, X->woff, gsync);
+              exchange(ls, wa, ra, X->roff, X->woff, gsync);
+            }
           } break;
           default: break;
         }
@@ -689,12 +771,16 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
         cfa = ncfa;
       }
       // ================= input gradients of this group's samples =================
+      if constexpr (CL) {   // publish this warp's partial sums to the cluster scratch
+        for (int i = lane; i < a.n_inputs; i += 32) __stcg(cred + (size_t)gw * 48 + 16 + i, gxacc[i]);
+      }
       gsync();
       if (a.gx != nullptr && gw == 0) {
         for (int i = lane; i < spw * a.n_inputs; i += 32) {
           const long long bb = wb * spw + i / a.n_inputs;
           float t = 0.f;
-          for (int w = 0; w < gwarps; ++w) t += gxacc[(size_t)w * spw * max(a.n_inputs, 1) + i];   // the group's warps, fixed order
+          for (int w = 0; w < gwarps; ++w)                                   // the group's warps, fixed order
+            t += CL ? __ldcg(cred + (size_t)w * 48 + 16 + i) : gxacc[(size_t)w * spw * max(a.n_inputs, 1) + i];
           if (bb < a.B) a.gx[(size_t)bb * a.n_inputs + (i % a.n_inputs)] = t;
         }
       }
@@ -705,7 +791,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
 
   if constexpr (BWD) {
     __syncthreads();
-    for (int i = threadIdx.x; i < a.n_acc; i += THREADS) {
+    for (int i = threadIdx.x; i < a.n_acc; i += blockDim.x) {
       float s = 0.f;
 #pragma unroll 1
       for (int w = 0; w < WARPS; ++w) s += S.wacc[(size_t)w * a.n_acc + i];
@@ -808,10 +894,17 @@ void fill_args(const qnn_circuit* c, const Program& p, const Plan& pl, void* ws,
   a->big = reinterpret_cast<const float2*>(wsb + pl.ws_coef); a->n_big = p.n_big_tables;
   a->small = a->big + (size_t)p.n_big_tables * 32 * G; a->n_small = p.n_small_tables;
   a->n = p.n; a->tb = p.tb; a->wb = p.wb; a->n_inputs = c->n_inputs; a->n_acc = p.n_acc;
-  a->table_bytes = (unsigned)table_bytes(p, c->n_inputs, (bwd ? kBwdThreads : kFwdThreads) / 32, bwd);
+  a->cluster = pl.cluster;
+  const int threads = bwd ? kBwdThreads : pl.fwd_threads;
+  a->table_bytes = (unsigned)table_bytes(p, c->n_inputs, threads / 32, bwd, pl.cluster > 0);
   for (int b = 0; b < 16; ++b) a->wire_of_bit[b] = 0;
   for (int w = 0; w < p.n; ++w) a->wire_of_bit[p.final_bit_of_wire[w]] = (int8_t)w;
   a->partial = reinterpret_cast<float*>(wsb + pl.ws_coef + pl.ws_diag);
+  if (pl.cluster > 0) {
+    unsigned char* cb = wsb + pl.ws_coef + pl.ws_diag + pl.ws_partial;
+    a->cbuf = cb;
+    a->cred = reinterpret_cast<float*>(cb + ((size_t)pl.n_clusters << (p.n + 5)));
+  }
 }
 
 int launch_prep(const Program& p, const float* w, const VmArgs& a, cudaStream_t st) {
@@ -836,24 +929,47 @@ size_t state_bytes(const Program& p, int64_t B) {
   return (size_t)n_batches(p, B) * ((size_t)kWarpAmps << p.wb) * sizeof(float2);
 }
 
+// How many clusters of `cluster` CTAs can be resident at once (GPC boundaries strand some SMs, so this is
+// less than 148 / cluster); a persistent cluster beyond that number would run as a second wave.
+static int max_active_clusters(int cluster, size_t smem);
+
 bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
   if (!p.ok) return false;
-  if ((kBwdThreads / 32) >> p.wb == 0) return false;            // a sample must fit the warps of one CTA
-  out->fwd_threads = kFwdThreads;
-  size_t sf = smem_bytes(p, c->n_inputs, kFwdThreads / 32, false);
-  if (sf > kSmemMax && p.wb > 0) {                               // large samples: fewer groups per CTA
-    out->fwd_threads = kBwdThreads;
-    sf = smem_bytes(p, c->n_inputs, kBwdThreads / 32, false);
-  }
-  const size_t sb = smem_bytes(p, c->n_inputs, kBwdThreads / 32, true);
-  if (sf > kSmemMax || sb > kSmemMax) return false;
+  const int bwd_warps = kBwdThreads / 32;
+  out->cluster = 0; out->n_clusters = 0; out->ws_cluster = 0;
   out->threads = kBwdThreads;
-  out->warps_per_cta = kBwdThreads / 32;
-  out->smem_fwd = sf;
-  out->smem_bwd = sb;
-  const int64_t groups_per_cta = (kBwdThreads / 32) >> p.wb;
-  const int64_t ctas = (n_batches(p, B) + groups_per_cta - 1) / groups_per_cta;
-  out->grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, 148));   // backward: one CTA per SM
+  out->warps_per_cta = bwd_warps;
+  if ((1 << p.wb) > bwd_warps) {
+    // a sample needs the registers of several SMs: thread-block cluster of 2^wb / 8 CTAs (2, 4, 8)
+    out->cluster = (1 << p.wb) / bwd_warps;
+    // Measured (profiles/experiments/n16.py): with 2 CTAs per sample (n = 14) the cluster geometry beats
+    // the generic kernels 14.6 % to 8.9 % of the roofline; with 4 and 8 CTAs the all-to-all exchange through
+    // L2 is transaction-bound (25 sectors per request: a transposition cannot be coalesced on both sides
+    // without staging) and the generic kernels are ahead, so those sizes stay there unless asked for.
+    static const bool all_clusters = [] { const char* e = getenv("QNN_VM_ALL_CLUSTERS"); return e && e[0] == '1'; }();
+    if (out->cluster > 2 && !all_clusters) return false;
+    out->fwd_threads = kBwdThreads;
+    out->smem_fwd = smem_bytes(p, c->n_inputs, bwd_warps, false, true);
+    out->smem_bwd = smem_bytes(p, c->n_inputs, bwd_warps, true, true);
+    if (out->smem_fwd > kSmemMax || out->smem_bwd > kSmemMax) return false;
+    out->n_clusters = (int)std::max<int64_t>(1, std::min<int64_t>(B, max_active_clusters(out->cluster, out->smem_bwd)));
+    out->grid = out->n_clusters * out->cluster;
+    out->ws_cluster = align256(((size_t)out->n_clusters << (p.n + 5)) + (size_t)out->n_clusters * (1 << p.wb) * 48 * sizeof(float));
+  } else {
+    out->fwd_threads = kFwdThreads;
+    size_t sf = smem_bytes(p, c->n_inputs, kFwdThreads / 32, false, false);
+    if (sf > kSmemMax && p.wb > 0) {                               // large samples: fewer groups per CTA
+      out->fwd_threads = kBwdThreads;
+      sf = smem_bytes(p, c->n_inputs, bwd_warps, false, false);
+    }
+    const size_t sb = smem_bytes(p, c->n_inputs, bwd_warps, true, false);
+    if (sf > kSmemMax || sb > kSmemMax) return false;
+    out->smem_fwd = sf;
+    out->smem_bwd = sb;
+    const int64_t groups_per_cta = bwd_warps >> p.wb;
+    const int64_t ctas = (n_batches(p, B) + groups_per_cta - 1) / groups_per_cta;
+    out->grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, 148));   // backward: one CTA per SM
+  }
   out->ws_coef = align256(std::max<size_t>(p.coef_ops.size(), 1) * QNN_COEF_STRIDE * sizeof(float));
   out->ws_diag = align256(((size_t)p.n_big_tables * (1024u << p.wb) + (size_t)p.n_small_tables * 32 + 1) * sizeof(float2));
   out->ws_partial = align256((size_t)out->grid * std::max(p.n_acc, 1) * sizeof(float));
@@ -901,27 +1017,66 @@ void release(Program* p) {
   p->d_exchanges = nullptr; p->d_xbase = nullptr; p->d_slots = nullptr; p->d_slot_ptr = nullptr; p->d_slot_idx = nullptr;
 }
 
+// Plain launch, or a cluster launch (cudaLaunchKernelEx) when a sample spans several CTAs.
+template <typename K>
+int launch_vm(K kern, const Plan& pl, int grid, int threads, size_t smem, const VmArgs& a, cudaStream_t st) {
+  int r = set_smem(kern, smem);
+  if (r) return r;
+  if (pl.cluster == 0) {
+    kern<<<grid, threads, smem, st>>>(a);
+  } else {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(threads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr{};
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = pl.cluster; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr; cfg.numAttrs = 1;
+    QNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, a));
+  }
+  QNN_CUDA_CHECK(cudaGetLastError());
+  return QNN_OK;
+}
+
+static int max_active_clusters(int cluster, size_t smem) {
+  static int cache[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  if (cluster < 1 || cluster > 8) return 1;
+  if (cache[cluster] > 0) return cache[cluster];
+  int n = 148 / cluster;
+  auto kern = k_vm<true, kBwdThreads, 1, false, 2>;
+  if (smem <= kSmemMax && cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemMax) == cudaSuccess) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(148 / cluster * cluster); cfg.blockDim = dim3(kBwdThreads); cfg.dynamicSmemBytes = smem;
+    cudaLaunchAttribute attr{};
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = cluster; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr; cfg.numAttrs = 1;
+    int q = 0;
+    if (cudaOccupancyMaxActiveClusters(&q, kern, &cfg) == cudaSuccess && q > 0) n = std::min(n, q);
+    else (void)cudaGetLastError();
+  } else {
+    (void)cudaGetLastError();
+  }
+  cache[cluster] = n;
+  return n;
+}
+
 int forward(const qnn_circuit* c, const Program& p, const Plan& pl, const float* x, const float* w, float* y,
             int64_t B, void* ws, float* state, cudaStream_t st) {
   VmArgs a{};
   fill_args(c, p, pl, ws, false, &a);
-  a.table_bytes = (unsigned)table_bytes(p, c->n_inputs, pl.fwd_threads / 32, false);
   a.x = x; a.y = y; a.B = B; a.state = reinterpret_cast<float4*>(state);
   int rc = launch_prep(p, w, a, st);
   if (rc) return rc;
-  const int64_t groups_per_cta = (pl.fwd_threads / 32) >> p.wb;
-  const int64_t ctas = (n_batches(p, B) + groups_per_cta - 1) / groups_per_cta;
-  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, 148));
-  auto go = [&](auto kern, int threads) -> int {
-    int r = set_smem(kern, pl.smem_fwd);
-    if (r) return r;
-    kern<<<grid, threads, pl.smem_fwd, st>>>(a);
-    QNN_CUDA_CHECK(cudaGetLastError());
-    return QNN_OK;
-  };
-  if (p.wb == 0) return a.state ? go(k_vm<false, kFwdThreads, 1, true, false>, kFwdThreads) : go(k_vm<false, kFwdThreads, 1, false, false>, kFwdThreads);
-  if (pl.fwd_threads == kFwdThreads) return a.state ? go(k_vm<false, kFwdThreads, 1, true, true>, kFwdThreads) : go(k_vm<false, kFwdThreads, 1, false, true>, kFwdThreads);
-  return a.state ? go(k_vm<false, kBwdThreads, 1, true, true>, kBwdThreads) : go(k_vm<false, kBwdThreads, 1, false, true>, kBwdThreads);
+  int grid = pl.grid;
+  if (pl.cluster == 0) {
+    const int64_t groups_per_cta = (pl.fwd_threads / 32) >> p.wb;
+    const int64_t ctas = (n_batches(p, B) + groups_per_cta - 1) / groups_per_cta;
+    grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, 148));
+  }
+  auto go = [&](auto kern) { return launch_vm(kern, pl, grid, pl.fwd_threads, pl.smem_fwd, a, st); };
+  if (pl.cluster > 0) return a.state ? go(k_vm<false, kFwdThreads, 1, true, 2>) : go(k_vm<false, kFwdThreads, 1, false, 2>);
+  if (p.wb > 0) return a.state ? go(k_vm<false, kFwdThreads, 1, true, 1>) : go(k_vm<false, kFwdThreads, 1, false, 1>);
+  return a.state ? go(k_vm<false, kFwdThreads, 1, true, 0>) : go(k_vm<false, kFwdThreads, 1, false, 0>);
 }
 
 int backward(const qnn_circuit* c, const Program& p, const Plan& pl, const float* x, const float* w,
@@ -931,15 +1086,10 @@ int backward(const qnn_circuit* c, const Program& p, const Plan& pl, const float
   a.x = x; a.gy = gy; a.gx = gx; a.B = B; a.state = reinterpret_cast<float4*>(const_cast<float*>(state));
   int rc = launch_prep(p, w, a, st);
   if (rc) return rc;
-  auto go = [&](auto kern) -> int {
-    int r = set_smem(kern, pl.smem_bwd);
-    if (r) return r;
-    kern<<<pl.grid, kBwdThreads, pl.smem_bwd, st>>>(a);
-    QNN_CUDA_CHECK(cudaGetLastError());
-    return QNN_OK;
-  };
-  if (p.wb == 0) rc = a.state ? go(k_vm<true, kBwdThreads, 1, true, false>) : go(k_vm<true, kBwdThreads, 1, false, false>);
-  else rc = a.state ? go(k_vm<true, kBwdThreads, 1, true, true>) : go(k_vm<true, kBwdThreads, 1, false, true>);
+  auto go = [&](auto kern) { return launch_vm(kern, pl, pl.grid, kBwdThreads, pl.smem_bwd, a, st); };
+  if (pl.cluster > 0) rc = a.state ? go(k_vm<true, kBwdThreads, 1, true, 2>) : go(k_vm<true, kBwdThreads, 1, false, 2>);
+  else if (p.wb > 0) rc = a.state ? go(k_vm<true, kBwdThreads, 1, true, 1>) : go(k_vm<true, kBwdThreads, 1, false, 1>);
+  else rc = a.state ? go(k_vm<true, kBwdThreads, 1, true, 0>) : go(k_vm<true, kBwdThreads, 1, false, 0>);
   if (rc) return rc;
   if (c->n_weights > 0) {
     k_vm_finalize<<<c->n_weights, 128, 0, st>>>(a.partial, pl.grid, p.n_acc, p.d_slots, p.d_slot_ptr, p.d_slot_idx, gw);

@@ -4,7 +4,9 @@
 // Geometry: every thread keeps 2^R = 32 complex amplitudes of one sample in registers (R = 5 "register
 // bits"); 2^TB threads share a sample (TB = n - 5 "thread bits", n = 5..13): for n <= 10 these are lanes of
 // one warp, which then carries 32 / 2^TB samples and always 1024 amplitudes; for n = 11..13 a sample spans
-// 2^(n-10) warps of one CTA (a "group"), which exchange through a group-wide shared buffer and a named barrier.  A *layout* says which logical wire sits on which
+// 2^(n-10) warps of one CTA (a "group"), which exchange through a group-wide shared buffer and a named barrier;
+// for n = 14..16 the group is a thread-block cluster of 2..8 CTAs (a sample needs the registers of several
+// SMs), exchanging through an L2-resident buffer in the workspace with cluster barriers.  A *layout* says which logical wire sits on which
 // physical bit; gates act only on register bits, and an EXCHANGE micro-op re-lays the state out
 // through a warp-private shared-memory buffer with GF(2)-linear, bank-conflict-free addressing.
 // CNOTs cost nothing: they update the layout matrix and are materialised by the next exchange.
@@ -22,8 +24,8 @@ namespace vm {
 constexpr int kR = 5;                  // register bits
 constexpr int kAmps = 1 << kR;         // amplitudes per thread
 constexpr int kWarpAmps = 1024;        // amplitudes per warp (any TB)
-constexpr int kMinQubits = 5, kMaxQubits = 13;
-constexpr int kMaxThreadBits = kMaxQubits - kR;   // 8
+constexpr int kMinQubits = 5, kMaxQubits = 16;
+constexpr int kMaxThreadBits = kMaxQubits - kR;   // 11
 
 enum MopKind : int32_t {
   MOP_END = 0,
@@ -112,6 +114,8 @@ std::string describe(const Program& p);   // JSON, for tests and introspection
 
 struct Plan {
   int threads, grid, warps_per_cta, fwd_threads;
+  int cluster, n_clusters;               // CTAs per sample for n >= 14 (0: no cluster), clusters in the grid
+  size_t ws_cluster;                     // exchange buffers + cross-CTA scratch of the cluster geometry
   size_t smem_fwd, smem_bwd;
   size_t ws_coef, ws_diag, ws_partial;   // bytes (each 256-aligned)
 };

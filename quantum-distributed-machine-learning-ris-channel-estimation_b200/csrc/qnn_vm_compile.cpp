@@ -321,8 +321,8 @@ struct Builder {
     uint32_t acol[16];
     for (int w = 0; w < n; ++w) acol[new_bit_of_wire[w]] = inv_col[w];
     for (int b = n; b < E; ++b) acol[b] = 1u << b;
-    // slot map S (columns scol[e], E bits), bank-conflict-free for 64-bit accesses on both sides:
-    // the low 4 slot bits must be a bijection of lane bits 0..3 (extended bits 5..8) for writer and reader
+    // slot map S (columns scol[e], E bits), random invertible GF(2) matrix, accepted when both the writing
+    // and the reading side are well-behaved: the low slot bits must be a bijection of the lane bits
     Lcg rng{0x9E3779B97F4A7C15ULL + P->exchanges.size() * 7919ULL};
     uint32_t scol[16], rcol[16];
     const uint32_t emask = (1u << E) - 1u;
@@ -335,9 +335,15 @@ struct Builder {
         for (int e = 0; e < E; ++e) if ((acol[b] >> e) & 1u) s ^= scol[e];
         rcol[b] = s;
       }
-      uint32_t wlow[4], rlow[4];
-      for (int i = 0; i < 4; ++i) { wlow[i] = scol[5 + i] & 15u; rlow[i] = rcol[5 + i] & 15u; }
-      if (independent(wlow, 4) && independent(rlow, 4)) break;
+      if (P->wb <= 3) {   // shared-memory buffer: no bank conflicts within a half-warp
+        uint32_t wlow[4], rlow[4];
+        for (int i = 0; i < 4; ++i) { wlow[i] = scol[5 + i] & 15u; rlow[i] = rcol[5 + i] & 15u; }
+        if (independent(wlow, 4) && independent(rlow, 4)) break;
+      } else {            // L2 buffer of the cluster geometry: the 32 lanes of a warp cover one aligned 256-byte block
+        uint32_t wlow[5], rlow[5];
+        for (int i = 0; i < 5; ++i) { wlow[i] = scol[5 + i] & 31u; rlow[i] = rcol[5 + i] & 31u; }
+        if (independent(wlow, 5) && independent(rlow, 5)) break;
+      }
     }
     Exchange X{};
     const int G = 32 << P->wb;
@@ -445,7 +451,7 @@ struct Builder {
     n = c->n_qubits;
     tb = n - kR;
     P->n = n; P->tb = tb; P->wb = n > 10 ? n - 10 : 0;
-    if (n < kMinQubits || n > kMaxQubits) { P->why_not = "n_qubits outside [5, 13]"; return false; }
+    if (n < kMinQubits || n > kMaxQubits) { P->why_not = "n_qubits outside [5, 16]"; return false; }
     if (c->encoder != QNN_ENC_NONE) { P->why_not = "amplitude encoder"; return false; }
     if (c->n_inputs > 32) { P->why_not = "more than 32 input columns"; return false; }
     if (!lower_items()) return false;
