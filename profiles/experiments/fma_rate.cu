@@ -74,6 +74,23 @@ __global__ void __launch_bounds__(THREADS) k(float* out, const float* in, int it
           a[i + 16] = __ffma2_rn(s2, a[i], a[i + 16]);
           a[i] = __ffma2_rn(c2, a[i + 16], a[i]);
         }
+      } else if (MODE == 10) {  // rotation-gradient contraction: acc += l[j1] (.) p[j0] (three pair operands), 4 chains
+        float2 v0[4], v1[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { v0[k] = make_float2(0.f, 0.f); v1[k] = make_float2(0.f, 0.f); }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          v0[i & 3] = __ffma2_rn(a[2 * i + 17 > 31 ? 31 : 2 * i + 17], a[2 * i], v0[i & 3]);
+          v1[i & 3] = __ffma2_rn(a[2 * i + 16], a[2 * i + 1], v1[i & 3]);
+        }
+        a[0] = __fadd2_rn(a[0], __fadd2_rn(__fadd2_rn(v0[0], v0[1]), __fadd2_rn(v0[2], v0[3])));
+        a[1] = __fadd2_rn(a[1], __fadd2_rn(__fadd2_rn(v1[0], v1[1]), __fadd2_rn(v1[2], v1[3])));
+      } else if (MODE == 11) {  // unit-phase multiply in place: a = er*a + (-ei,ei) (.) swap(a)   (DIAG / CU3 phases)
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const float2 sw = make_float2(a[i].y, a[i].x);
+          a[i] = __ffma2_rn(ui, sw, __fmul2_rn(ur, a[i]));
+        }
       } else if (MODE == 7) {  // packed general complex 2x2 on bit 0 (first row only + second row): 8 packed + 4 swaps / pair
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
@@ -103,7 +120,7 @@ void run(const char* name, float* d_out, float* d_in, int ctas_per_sm) {
   k<MODE, THREADS><<<grid, THREADS>>>(d_out, d_in, iters, 0.999f, 1e-4f);
   cudaEventRecord(e1); cudaEventSynchronize(e1);
   float ms; cudaEventElapsedTime(&ms, e0, e1);
-  const double per_iter = (MODE == 8 || MODE == 9) ? 96.0 : 128.0;     // scalar-equivalent FMA-pipe instructions
+  const double per_iter = (MODE == 8 || MODE == 9) ? 96.0 : (MODE == 10 ? 48.0 : 128.0);   // scalar-equivalent FMA-pipe instructions
   const double instr = (double)grid * (THREADS / 32) * iters * per_iter;
   const double per_clk_smsp = instr / (ms * 1e-3 * 1.965e9) / (148 * 4);
   printf("%-34s threads=%4d ctas/sm=%d: %.3f ms, %.3f FMA-pipe instr/clk/SMSP\n", name, THREADS, ctas_per_sm, ms, per_clk_smsp);
@@ -131,5 +148,9 @@ int main() {
   run<8, 256>("packed shear rot bit0", d_out, d_in, 1);
   run<9, 256>("packed shear rot bit4", d_out, d_in, 2);
   run<9, 128>("packed shear rot bit4", d_out, d_in, 1);
+  run<10, 256>("packed grad contraction (3 pairs)", d_out, d_in, 2);
+  run<10, 256>("packed grad contraction (3 pairs)", d_out, d_in, 1);
+  run<11, 256>("packed phase multiply (swap+2)", d_out, d_in, 2);
+  run<11, 256>("packed phase multiply (swap+2)", d_out, d_in, 1);
   return 0;
 }

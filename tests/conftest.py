@@ -10,6 +10,11 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    # The host-logic tests load libqnn_b200.so (no compute without a GPU): build it once if it is missing.
+    lib = os.path.join(ROOT, "quantum-distributed-machine-learning-ris-channel-estimation_b200", "libqnn_b200.so")
+    if not os.path.exists(lib):
+        import __graft_entry__
+        __graft_entry__.build()
 
 
 def pytest_collection_modifyitems(config, items):
