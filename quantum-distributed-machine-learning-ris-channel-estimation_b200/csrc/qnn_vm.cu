@@ -57,9 +57,10 @@ __device__ __forceinline__ void lds64(uint32_t addr, float& a, float& b) {
 __device__ __forceinline__ void stg64(unsigned char* base, uint32_t off, float a, float b) {
   __stcg(reinterpret_cast<float2*>(base + off), make_float2(a, b));
 }
+// Plain (L1-allocating) load: only ever issued after the cluster barrier's acquire, which makes the other
+// CTAs' stores visible whatever the cache policy; a reader's neighbouring registers share 32-byte sectors.
 __device__ __forceinline__ void ldg64(const unsigned char* base, uint32_t off, float& a, float& b) {
-  const float2 v = __ldcg(reinterpret_cast<const float2*>(base + off));
-  a = v.x; b = v.y;
+  asm volatile("ld.global.v2.f32 {%0, %1}, [%2];" : "=f"(a), "=f"(b) : "l"(base + off) : "memory");
 }
 
 template <int RB>
@@ -942,12 +943,6 @@ bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
   if ((1 << p.wb) > bwd_warps) {
     // a sample needs the registers of several SMs: thread-block cluster of 2^wb / 8 CTAs (2, 4, 8)
     out->cluster = (1 << p.wb) / bwd_warps;
-    // Measured (profiles/experiments/n16.py): with 2 CTAs per sample (n = 14) the cluster geometry beats
-    // the generic kernels 14.6 % to 8.9 % of the roofline; with 4 and 8 CTAs the all-to-all exchange through
-    // L2 is transaction-bound (25 sectors per request: a transposition cannot be coalesced on both sides
-    // without staging) and the generic kernels are ahead, so those sizes stay there unless asked for.
-    static const bool all_clusters = [] { const char* e = getenv("QNN_VM_ALL_CLUSTERS"); return e && e[0] == '1'; }();
-    if (out->cluster > 2 && !all_clusters) return false;
     out->fwd_threads = kBwdThreads;
     out->smem_fwd = smem_bytes(p, c->n_inputs, bwd_warps, false, true);
     out->smem_bwd = smem_bytes(p, c->n_inputs, bwd_warps, true, true);

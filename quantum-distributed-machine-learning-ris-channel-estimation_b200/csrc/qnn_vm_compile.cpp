@@ -305,6 +305,11 @@ struct Builder {
     for (int w = 0; w < n && (int)order.size() < kR; ++w)
       if (is_unit(rowmask[w]) && ctz(rowmask[w]) < kR) add(w);
     for (int w = 0; w < n && (int)order.size() < kR; ++w) add(w);
+    if (P->wb > 3 && all_clean()) {
+      // cluster geometry: wires that now sit on lane bits take the low register bits, so that after the
+      // exchange a thread's registers 0..3 are consecutive slots of the L2 buffer (one 32-byte sector)
+      std::stable_partition(order.begin(), order.begin() + kR, [&](int w) { const int b = ctz(rowmask[w]); return b >= kR && b < 10; });
+    }
     std::vector<bool> used(n, false);
     for (int r = 0; r < kR; ++r) { bit_of_wire[order[r]] = r; used[order[r]] = true; }
     int b = kR;
@@ -329,21 +334,33 @@ struct Builder {
     for (int attempt = 0;; ++attempt) {
       if (attempt > 200000) { P->why_not = "internal: no conflict-free exchange found"; return false; }
       for (int e = 0; e < E; ++e) scol[e] = rng.next() & emask;
+      if (P->wb > 3) {
+        // L2 buffer: a warp's 32 lanes write one aligned 256-byte block: the low five slot bits are the lane
+        // bits.  (A transposition cannot be coalesced on the reading side as well; but when the wires coming
+        // onto register bits 0 and 1 were on lane bits, those lane bits become slot bits 0 and 1 and every
+        // reader's registers 0..3 share one 32-byte sector.)
+        int slot_of_lane[5] = {-1, -1, -1, -1, -1};
+        uint32_t taken = 0;
+        for (int b = 0; b < 2; ++b)
+          if (is_unit(acol[b])) {
+            const int e = ctz(acol[b]);
+            if (e >= 5 && e < 10) { slot_of_lane[e - 5] = b; taken |= 1u << b; }
+          }
+        for (int i = 0; i < 5; ++i)
+          if (slot_of_lane[i] < 0) { int b = 0; while ((taken >> b) & 1u) ++b; slot_of_lane[i] = b; taken |= 1u << b; }
+        for (int i = 0; i < 5; ++i) scol[5 + i] = 1u << slot_of_lane[i];
+      }
       if (!independent(scol, E)) continue;
       for (int b = 0; b < E; ++b) {
         uint32_t s = 0;
         for (int e = 0; e < E; ++e) if ((acol[b] >> e) & 1u) s ^= scol[e];
         rcol[b] = s;
       }
-      if (P->wb <= 3) {   // shared-memory buffer: no bank conflicts within a half-warp
-        uint32_t wlow[4], rlow[4];
-        for (int i = 0; i < 4; ++i) { wlow[i] = scol[5 + i] & 15u; rlow[i] = rcol[5 + i] & 15u; }
-        if (independent(wlow, 4) && independent(rlow, 4)) break;
-      } else {            // L2 buffer of the cluster geometry: the 32 lanes of a warp cover one aligned 256-byte block
-        uint32_t wlow[5], rlow[5];
-        for (int i = 0; i < 5; ++i) { wlow[i] = scol[5 + i] & 31u; rlow[i] = rcol[5 + i] & 31u; }
-        if (independent(wlow, 5) && independent(rlow, 5)) break;
-      }
+      if (P->wb > 3) break;
+      // shared-memory buffer: no bank conflicts within a half-warp, writing and reading
+      uint32_t wlow[4], rlow[4];
+      for (int i = 0; i < 4; ++i) { wlow[i] = scol[5 + i] & 15u; rlow[i] = rcol[5 + i] & 15u; }
+      if (independent(wlow, 4) && independent(rlow, 4)) break;
     }
     Exchange X{};
     const int G = 32 << P->wb;

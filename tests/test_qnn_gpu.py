@@ -10,7 +10,6 @@ import qris_b200
 from helpers import REL_TOL, assert_close, oracle_ops, seeded_inputs
 from oracle import qnn_oracle as O
 
-os.environ.setdefault("QNN_VM_ALL_CLUSTERS", "1")   # exercise the 4- and 8-CTA cluster geometry too (see test_largest_sizes)
 pytestmark = pytest.mark.gpu
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "qnn_golden.npz")
 
@@ -63,9 +62,7 @@ def test_cta_per_sample_sizes(n, L, B):
 @pytest.mark.parametrize("n,B", [(14, 2), (14, 80), (15, 3), (16, 1), (16, 20)])
 def test_largest_sizes(n, B):
     """n = 16 is QNN_MAX_QUBITS (BASELINE config 4's width): 512 KiB of state per sample, held in the
-    registers of a thread-block cluster (2 / 4 / 8 CTAs for n = 14 / 15 / 16).  Clusters of 4 and 8 are
-    slower than the generic kernels today, so they are opt-in (QNN_VM_ALL_CLUSTERS=1, read once per
-    process: this file sets it on import, before the library plans its first large circuit)."""
+    registers of a thread-block cluster (2 / 4 / 8 CTAs for n = 14 / 15 / 16)."""
     circ = qris_b200.u3cu3_circuit(n, 1)
     assert _plan(circ, B) == "vm-register"
     check_against_oracle(circ, B, seed=n)

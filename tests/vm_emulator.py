@@ -42,7 +42,14 @@ def _apply_reg(state, U, rbit, lane_mask=None, ctrl_rbit=None):
     state[np.ix_(lanes, j1)] = U[1, 0] * a0 + U[1, 1] * a1
 
 
-def check_conflict_free(base, off):
+def check_conflict_free(base, off, writing=True):
+    if len(base) > 32 * 8:                            # cluster geometry: L2 buffer; writes must be coalesced
+        if writing:
+            for j in range(0, 32, 5):
+                for w0 in range(0, len(base), 32):
+                    blocks = {(base[l] ^ off[j]) // 256 for l in range(w0, w0 + 32)}
+                    assert len(blocks) == 1, "a warp's exchange write is not one aligned 256-byte block"
+        return
     for j in range(32):
         for half in range(0, len(base), 16):          # every half-warp of every warp of the group
             slots = {((base[l] ^ off[j]) // 8) % 16 for l in range(half, half + 16)}
@@ -122,7 +129,7 @@ def emulate_forward(desc, x, w):
         elif kind == MOP_XCHG:
             X = desc["exchanges"][idx]
             check_conflict_free(X["wbase"], X["woff"])
-            check_conflict_free(X["rbase"], X["roff"])
+            check_conflict_free(X["rbase"], X["roff"], writing=False)
             buf = {}
             for l in range(G):
                 for jj in range(32):
