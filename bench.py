@@ -68,7 +68,7 @@ class ClockSampler:
               "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.marks = index, [], None, []
 
     def __enter__(self):
         try:
@@ -85,7 +85,11 @@ class ClockSampler:
         for line in self.proc.stdout:
             parts = [p.strip() for p in line.split(",")]
             if len(parts) >= 7:
-                self.rows.append(parts)
+                self.rows.append((time.time(), parts))
+
+    def mark(self):
+        """Call at the start and at the end of the timed region."""
+        self.marks.append(time.time())
 
     def __exit__(self, *exc):
         if self.proc is not None:
@@ -98,7 +102,15 @@ class ClockSampler:
 
     def summary(self):
         sm, mx, reasons = [], [], set()
-        for r in self.rows:
+        rows = self.rows
+        window = "timed region"
+        if len(self.marks) >= 2:
+            inside = [r for r in rows if self.marks[0] <= r[0] <= self.marks[-1] + 0.1]
+            if inside:
+                rows = inside
+            else:   # region shorter than the sampling period: use the samples taken under the same load (warm-up)
+                window = "warm-up + timed region (timed region shorter than the sampling period)"
+        for _, r in rows:
             try:
                 sm.append(float(r[0])); mx.append(float(r[1]))
             except ValueError:
@@ -108,7 +120,8 @@ class ClockSampler:
                     reasons.add(name)
         if not sm:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"], "samples": 0}
-        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm),
+                "window": window}
 
 
 # ---- CPU arm: the reference's execution model restated (oracle/, complex64, all host cores) ----------
@@ -267,16 +280,18 @@ def run_b200(args, wl):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
-        step()
-    barrier()
-    with ClockSampler(local_rank) as clocks:
+    with ClockSampler(local_rank) as clocks:                          # started early: nvidia-smi needs a moment
+        for _ in range(max(args.warmup, 3)):
+            step()
+        barrier()
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
         barrier()
+        clocks.mark()
         for s, e in ev:
             flush.zero_()                                             # L2 flush, outside the timed events
             s.record(); step(); e.record()
         barrier()
+        clocks.mark()
         step_ms = [s.elapsed_time(e) for s, e in ev]
         total_ms = sum(step_ms)
         # dominant kernel (adjoint backward) and the forward kernel, timed alone on the same stream
