@@ -37,6 +37,9 @@ struct VmArgs {
   const uint32_t* xbase; int n_xbase;       // per-thread exchange bases
   unsigned table_bytes;                     // shared-memory bytes of all tables (to place them around the buffers)
   int cluster;                              // CTAs per sample (cluster geometry), else 0
+  int amplitude;                            // amplitude encoder (GEOM 0 only): x row -> initial state
+  int n_angle;                              // input columns used as angles (0 with the amplitude encoder)
+  int8_t init_bit_of_wire[16];              // initial layout (amplitude encoder)
   unsigned char* cbuf;                      // cluster geometry: [clusters][2^n * 8] exchange buffers (workspace)
   float* cred;                              // cluster geometry: [clusters][group warps][48] cross-CTA partials
   int8_t wire_of_bit[16];                   // final (measurement) layout
@@ -446,11 +449,11 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
     float2* sbig = wbits == 0 ? reinterpret_cast<float2*>(take((size_t)a.n_big * 32 * G * sizeof(float2))) : nullptr;
     S.big = wbits == 0 ? sbig : a.big;
     S.small = reinterpret_cast<float2*>(take((size_t)a.n_small * 32 * sizeof(float2)));
-    S.xcoef = reinterpret_cast<float2*>(take((size_t)WARPS * spw * max(a.n_inputs, 1) * sizeof(float2)));
+    S.xcoef = reinterpret_cast<float2*>(take((size_t)WARPS * spw * max(a.n_angle, 1) * sizeof(float2)));
     S.red = reinterpret_cast<float*>(take((size_t)WARPS * 16 * sizeof(float)));
     if (BWD) {
       S.wacc = reinterpret_cast<float*>(take((size_t)WARPS * max(a.n_acc, 1) * sizeof(float)));
-      S.gxacc = reinterpret_cast<float*>(take((size_t)WARPS * spw * max(a.n_inputs, 1) * sizeof(float)));
+      S.gxacc = reinterpret_cast<float*>(take((size_t)WARPS * spw * max(a.n_angle, 1) * sizeof(float)));
     }
     const int tid = threadIdx.x;
     const uint32_t* src; uint32_t* dst; int words;
@@ -466,12 +469,12 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
     for (int i = tid; i < a.n_small * 32; i += blockDim.x) S.small[i] = a.small[i];
     if (BWD) {
       for (int i = tid; i < WARPS * max(a.n_acc, 1); i += blockDim.x) S.wacc[i] = 0.f;
-      for (int i = tid; i < WARPS * spw * max(a.n_inputs, 1); i += blockDim.x) S.gxacc[i] = 0.f;
+      for (int i = tid; i < WARPS * spw * max(a.n_angle, 1); i += blockDim.x) S.gxacc[i] = 0.f;
     }
   }
   __syncthreads();
   float* const wacc = BWD ? S.wacc + (size_t)warp * max(a.n_acc, 1) : nullptr;
-  float* const gxacc = BWD ? S.gxacc + (size_t)warp * spw * max(a.n_inputs, 1) : nullptr;
+  float* const gxacc = BWD ? S.gxacc + (size_t)warp * spw * max(a.n_angle, 1) : nullptr;
   float* const red = S.red + (size_t)warp * 16;
   // barrier over the threads that share one exchange buffer
   auto gsync = [&]() {
@@ -487,7 +490,11 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
   unsigned xpar = 0;
   float* const cred = CL ? a.cred + (size_t)cid * gwarps * 48 : nullptr;
 
-  float2* const xcoef = S.xcoef + (size_t)warp * spw * max(a.n_inputs, 1);
+  float2* const xcoef = S.xcoef + (size_t)warp * spw * max(a.n_angle, 1);
+  const int n_ang = a.n_angle;
+  // amplitude encoder: logical index (wire 0 = most significant bit) of this thread's register j is klog_t | klog_j(j)
+  auto klog = [&](unsigned p) { unsigned k = 0; for (int w = 0; w < a.n; ++w) k |= ((p >> a.init_bit_of_wire[w]) & 1u) << (a.n - 1 - w); return k; };
+  const unsigned klog_t = (GEOM == 0 && a.amplitude) ? klog((unsigned)tis << kR) : 0u;
   float2 ps[NA];
   const long long n_batches = (a.B + spw - 1) / spw;
   for (long long wb = CL ? (long long)cid : (long long)blockIdx.x * groups + grp; wb < n_batches;
@@ -497,12 +504,12 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
     gsync();   // nothing of the previous batch (scratch, exchange buffer) is still being read
 
     // shear coefficients of the per-sample rotations RY(x[b, col]): each (sample, column) once per batch
-    for (int i = lane; i < spw * a.n_inputs; i += 32) {
-      const long long bb = wb * spw + i / a.n_inputs;
-      xcoef[i] = rot_coef_x(bb < a.B ? a.x[(size_t)bb * a.n_inputs + (i % a.n_inputs)] : 0.f);
+    for (int i = lane; i < spw * n_ang; i += 32) {
+      const long long bb = wb * spw + i / n_ang;
+      xcoef[i] = rot_coef_x(bb < a.B ? a.x[(size_t)bb * a.n_inputs + (i % n_ang)] : 0.f);
     }
     __syncwarp();
-    const float2* const xc = xcoef + siw * a.n_inputs;
+    const float2* const xc = xcoef + siw * n_ang;
 
     // Saved final state: [batch][j / 2][lane] float4 = amplitudes (2 * (j/2), 2 * (j/2) + 1) of that lane;
     // a warp reads or writes 512 contiguous bytes per instruction.
@@ -516,7 +523,23 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
     } else {
 #pragma unroll
     for (int j = 0; j < NA; ++j) ps[j] = make_float2(0.f, 0.f);
-    ps[0].x = tis == 0 ? 1.f : 0.f;
+    if (GEOM == 0 && a.amplitude) {
+      // |psi> = x / |x| (first 2^n entries of the row, zero padded), gathered into the initial layout
+      const float* xr = a.x + (size_t)(active ? bs : 0) * a.n_inputs;
+      float ss = 0.f;
+#pragma unroll
+      for (int j = 0; j < NA; ++j) {
+        const unsigned k = klog_t | klog((unsigned)j);
+        const float v = (active && (int)k < a.n_inputs) ? xr[k] : 0.f;
+        ps[j].x = v;
+        ss = fmaf(v, v, ss);
+      }
+      const float inv = rsqrtf(sample_sum(ss, lbits));
+#pragma unroll
+      for (int j = 0; j < NA; ++j) ps[j].x *= inv;
+    } else {
+      ps[0].x = tis == 0 ? 1.f : 0.f;
+    }
 
     // ================= forward program =================
     // One jump per micro-op (handler id = kind and register bits); the next op and its coefficient row
@@ -661,7 +684,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
           H_CASE_ROT(0) H_CASE_ROT(1) H_CASE_ROT(2) H_CASE_ROT(3) H_CASE_ROT(4)
 #undef H_CASE_ROT
 #define H_CASE_ROTX(RB) case H_ROTX + RB: { const float2 ab = xc[op.idx]; float v = rot_grad<RB>(ps, ls); rot<RB>(ps, -ab.x, -ab.y); rot<RB>(ls, -ab.x, -ab.y); \
-            v = sample_sum(v, lbits); if ((lane & ((1 << lbits) - 1)) == 0) gxacc[siw * a.n_inputs + op.idx] += v; } break;
+            v = sample_sum(v, lbits); if ((lane & ((1 << lbits) - 1)) == 0) gxacc[siw * n_ang + op.idx] += v; } break;
           H_CASE_ROTX(0) H_CASE_ROTX(1) H_CASE_ROTX(2) H_CASE_ROTX(3) H_CASE_ROTX(4)
 #undef H_CASE_ROTX
 #define CU3_REDUCE(A, ACC)                                                                                  \
@@ -707,7 +730,7 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
               float v = rot_grad<K>(ps, ls);                                                               \
               rot<K>(ps, -ab.x, -ab.y); rot<K>(ls, -ab.x, -ab.y);                                          \
               v = sample_sum(v, lbits);                                                                    \
-              if ((lane & ((1 << lbits) - 1)) == 0) gxacc[siw * a.n_inputs + col] += v;                    \
+              if ((lane & ((1 << lbits) - 1)) == 0) gxacc[siw * n_ang + col] += v;                          \
             }
             ROTX5_STEP(4) ROTX5_STEP(3) ROTX5_STEP(2) ROTX5_STEP(1) ROTX5_STEP(0)
 #undef ROTX5_STEP
@@ -772,21 +795,46 @@ __global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
         cfa = ncfa;
       }
       // ================= input gradients of this group's samples =================
+      if (GEOM == 0 && a.amplitude) {
+        // psi0 = x / |x|:  dL/dx = (g - psi0 (psi0 . g)) / |x|  with g = 2 Re(lam0), in the initial layout
+        if (a.gx != nullptr) {
+          const float* xr = a.x + (size_t)(active ? bs : 0) * a.n_inputs;
+          float* gxr = a.gx + (size_t)(active ? bs : 0) * a.n_inputs;
+          float xv[NA], ss = 0.f, dot = 0.f;
+#pragma unroll
+          for (int j = 0; j < NA; ++j) {
+            const unsigned k = klog_t | klog((unsigned)j);
+            xv[j] = (active && (int)k < a.n_inputs) ? xr[k] : 0.f;
+            ss = fmaf(xv[j], xv[j], ss);
+            dot = fmaf(xv[j], 2.f * ls[j].x, dot);
+          }
+          const float inv = rsqrtf(sample_sum(ss, lbits));
+          dot = sample_sum(dot, lbits) * inv;
+#pragma unroll
+          for (int j = 0; j < NA; ++j) {
+            const unsigned k = klog_t | klog((unsigned)j);
+            if (active && (int)k < a.n_inputs) gxr[k] = (2.f * ls[j].x - xv[j] * inv * dot) * inv;
+          }
+          if (active && a.n_inputs > (1 << a.n))          // columns beyond 2^n never enter the state
+            for (int k = (1 << a.n) + tis; k < a.n_inputs; k += (1 << tb)) gxr[k] = 0.f;
+        }
+        continue;
+      }
       if constexpr (CL) {   // publish this warp's partial sums to the cluster scratch
-        for (int i = lane; i < a.n_inputs; i += 32) __stcg(cred + (size_t)gw * 48 + 16 + i, gxacc[i]);
+        for (int i = lane; i < n_ang; i += 32) __stcg(cred + (size_t)gw * 48 + 16 + i, gxacc[i]);
       }
       gsync();
       if (a.gx != nullptr && gw == 0) {
-        for (int i = lane; i < spw * a.n_inputs; i += 32) {
-          const long long bb = wb * spw + i / a.n_inputs;
+        for (int i = lane; i < spw * n_ang; i += 32) {
+          const long long bb = wb * spw + i / n_ang;
           float t = 0.f;
           for (int w = 0; w < gwarps; ++w)                                   // the group's warps, fixed order
-            t += CL ? __ldcg(cred + (size_t)w * 48 + 16 + i) : gxacc[(size_t)w * spw * max(a.n_inputs, 1) + i];
-          if (bb < a.B) a.gx[(size_t)bb * a.n_inputs + (i % a.n_inputs)] = t;
+            t += CL ? __ldcg(cred + (size_t)w * 48 + 16 + i) : gxacc[(size_t)w * spw * max(n_ang, 1) + i];
+          if (bb < a.B) a.gx[(size_t)bb * a.n_inputs + (i % n_ang)] = t;
         }
       }
       gsync();
-      for (int i = lane; i < spw * a.n_inputs; i += 32) gxacc[i] = 0.f;
+      for (int i = lane; i < spw * n_ang; i += 32) gxacc[i] = 0.f;
     }
   }
 
@@ -896,8 +944,11 @@ void fill_args(const qnn_circuit* c, const Program& p, const Plan& pl, void* ws,
   a->small = a->big + (size_t)p.n_big_tables * 32 * G; a->n_small = p.n_small_tables;
   a->n = p.n; a->tb = p.tb; a->wb = p.wb; a->n_inputs = c->n_inputs; a->n_acc = p.n_acc;
   a->cluster = pl.cluster;
+  a->amplitude = p.amplitude ? 1 : 0;
+  a->n_angle = p.amplitude ? 0 : c->n_inputs;
+  for (int w = 0; w < 16; ++w) a->init_bit_of_wire[w] = w < p.n ? (int8_t)p.initial_bit_of_wire[w] : 0;
   const int threads = bwd ? kBwdThreads : pl.fwd_threads;
-  a->table_bytes = (unsigned)table_bytes(p, c->n_inputs, threads / 32, bwd, pl.cluster > 0);
+  a->table_bytes = (unsigned)table_bytes(p, p.amplitude ? 0 : c->n_inputs, threads / 32, bwd, pl.cluster > 0);
   for (int b = 0; b < 16; ++b) a->wire_of_bit[b] = 0;
   for (int w = 0; w < p.n; ++w) a->wire_of_bit[p.final_bit_of_wire[w]] = (int8_t)w;
   a->partial = reinterpret_cast<float*>(wsb + pl.ws_coef + pl.ws_diag);
@@ -937,6 +988,7 @@ static int max_active_clusters(int cluster, size_t smem);
 bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
   if (!p.ok) return false;
   const int bwd_warps = kBwdThreads / 32;
+  const int n_ang_in = p.amplitude ? 0 : c->n_inputs;        // input columns that need per-warp scratch
   out->cluster = 0; out->n_clusters = 0; out->ws_cluster = 0;
   out->threads = kBwdThreads;
   out->warps_per_cta = bwd_warps;
@@ -944,20 +996,20 @@ bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
     // a sample needs the registers of several SMs: thread-block cluster of 2^wb / 8 CTAs (2, 4, 8)
     out->cluster = (1 << p.wb) / bwd_warps;
     out->fwd_threads = kBwdThreads;
-    out->smem_fwd = smem_bytes(p, c->n_inputs, bwd_warps, false, true);
-    out->smem_bwd = smem_bytes(p, c->n_inputs, bwd_warps, true, true);
+    out->smem_fwd = smem_bytes(p, n_ang_in, bwd_warps, false, true);
+    out->smem_bwd = smem_bytes(p, n_ang_in, bwd_warps, true, true);
     if (out->smem_fwd > kSmemMax || out->smem_bwd > kSmemMax) return false;
     out->n_clusters = (int)std::max<int64_t>(1, std::min<int64_t>(B, max_active_clusters(out->cluster, out->smem_bwd)));
     out->grid = out->n_clusters * out->cluster;
     out->ws_cluster = align256(((size_t)out->n_clusters << (p.n + 5)) + (size_t)out->n_clusters * (1 << p.wb) * 48 * sizeof(float));
   } else {
     out->fwd_threads = kFwdThreads;
-    size_t sf = smem_bytes(p, c->n_inputs, kFwdThreads / 32, false, false);
+    size_t sf = smem_bytes(p, n_ang_in, kFwdThreads / 32, false, false);
     if (sf > kSmemMax && p.wb > 0) {                               // large samples: fewer groups per CTA
       out->fwd_threads = kBwdThreads;
-      sf = smem_bytes(p, c->n_inputs, bwd_warps, false, false);
+      sf = smem_bytes(p, n_ang_in, bwd_warps, false, false);
     }
-    const size_t sb = smem_bytes(p, c->n_inputs, bwd_warps, true, false);
+    const size_t sb = smem_bytes(p, n_ang_in, bwd_warps, true, false);
     if (sf > kSmemMax || sb > kSmemMax) return false;
     out->smem_fwd = sf;
     out->smem_bwd = sb;

@@ -83,6 +83,7 @@ struct GradSlot {      // gw[weight] += accumulator[acc]  (every gradient is a d
 struct Program {
   bool ok = false;
   std::string why_not;           // when !ok: why the VM does not take this circuit (generic path used)
+  bool amplitude = false;        // amplitude encoder: the (normalised) input row is the initial state (n <= 10)
   int n = 0, tb = 0;             // tb = n - 5 thread bits
   int wb = 0;                    // warp bits: max(0, n - 10); a group is 2^wb warps
   std::vector<MicroOp> ops;      // forward order, MOP_END-terminated

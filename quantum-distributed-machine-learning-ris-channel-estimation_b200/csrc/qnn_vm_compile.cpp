@@ -469,8 +469,9 @@ struct Builder {
     tb = n - kR;
     P->n = n; P->tb = tb; P->wb = n > 10 ? n - 10 : 0;
     if (n < kMinQubits || n > kMaxQubits) { P->why_not = "n_qubits outside [5, 16]"; return false; }
-    if (c->encoder != QNN_ENC_NONE) { P->why_not = "amplitude encoder"; return false; }
-    if (c->n_inputs > 32) { P->why_not = "more than 32 input columns"; return false; }
+    P->amplitude = c->encoder == QNN_ENC_AMPLITUDE;
+    if (P->amplitude && n > 10) { P->why_not = "amplitude encoder above 10 qubits"; return false; }
+    if (!P->amplitude && c->n_inputs > 32) { P->why_not = "more than 32 angle input columns"; return false; }
     if (!lower_items()) return false;
     int bits[16];
     for (int w = 0; w < n; ++w) rowmask[w] = 1u << w;   // provisional, only "unit-ness" matters here
@@ -591,7 +592,7 @@ std::string describe(const Program& p) {
   o.precision(9);
   o << "{\"ok\": " << (p.ok ? "true" : "false") << ", \"why_not\": \"" << p.why_not << "\"";
   if (!p.ok) { o << "}"; return o.str(); }
-  o << ", \"n\": " << p.n << ", \"tb\": " << p.tb << ", \"wb\": " << p.wb << ", \"n_acc\": " << p.n_acc;
+  o << ", \"amplitude\": " << (p.amplitude ? "true" : "false") << ", \"n\": " << p.n << ", \"tb\": " << p.tb << ", \"wb\": " << p.wb << ", \"n_acc\": " << p.n_acc;
   auto arr = [&](const char* name, const int* v, int cnt) {
     o << ", \"" << name << "\": [";
     for (int i = 0; i < cnt; ++i) o << (i ? ", " : "") << v[i];

@@ -53,6 +53,16 @@ def test_amplitude_encoder_parity(n, L, B):
     check_against_oracle(qris_b200.u3cu3_circuit(n, L, encoder="amplitude"), B, seed=n)
 
 
+@pytest.mark.parametrize("n,n_inputs,B", [(5, 32, 40), (6, 50, 33), (8, 256, 64), (8, 300, 7), (10, 1024, 20), (9, 1, 3)])
+def test_amplitude_encoder_on_the_vm(n, n_inputs, B):
+    """Rows shorter than 2^n are zero padded, longer ones truncated (their extra columns get zero
+    gradient); 8 qubits x 256 inputs is the raw (2, 16, 8) pilot tensor of Run:345."""
+    base = qris_b200.u3cu3_circuit(n, 2, encoder="amplitude")
+    circ = qris_b200.Circuit(n, base.ops, n_inputs=n_inputs, n_weights=base.n_weights, encoder="amplitude")
+    assert _plan(circ, B) == "vm-register"
+    check_against_oracle(circ, B, seed=n + n_inputs)
+
+
 @pytest.mark.parametrize("n,L,B", [(11, 2, 5), (12, 1, 3), (13, 1, 2)])
 def test_cta_per_sample_sizes(n, L, B):
     check_against_oracle(qris_b200.u3cu3_circuit(n, L), B, seed=n)

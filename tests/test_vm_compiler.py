@@ -18,7 +18,7 @@ def _check(circ, seed=0):
     x = rng.uniform(-1, 1, (spw, circ.n_inputs))
     w = rng.uniform(0, 2 * np.pi, circ.n_weights)
     y, stats = emulate_forward(desc, x, w)
-    yo = O.simulate(oracle_ops(circ), circ.n_qubits, torch.tensor(x), torch.tensor(w)).numpy()
+    yo = O.simulate(oracle_ops(circ), circ.n_qubits, torch.tensor(x), torch.tensor(w), encoder=circ.encoder).numpy()
     np.testing.assert_allclose(y, yo, atol=2e-7)   # constants travel as float32 (pi/2 of the RX lowering)
     return desc, stats
 
@@ -49,6 +49,13 @@ def test_multi_warp_samples(n, L):
         _check(qris_b200.u3cu3_circuit(n, 1), seed=n + 1)
 
 
+@pytest.mark.parametrize("n", [5, 8, 10])
+def test_amplitude_encoder_program(n):
+    """The (normalised) input row is the initial state, gathered into the program's initial layout."""
+    desc, _ = _check(qris_b200.u3cu3_circuit(n, 1, encoder="amplitude"), seed=n)
+    assert desc["amplitude"]
+
+
 def test_irregular_program():
     Op = qris_b200.Op
     n = 7
@@ -62,5 +69,5 @@ def test_irregular_program():
 
 def test_out_of_scope_circuits_report_why():
     assert not qris_b200.reference_circuit(4, 1).describe()["ok"]
-    d = qris_b200.u3cu3_circuit(6, 1, encoder="amplitude").describe()
+    d = qris_b200.u3cu3_circuit(12, 1, encoder="amplitude").describe()
     assert not d["ok"] and "amplitude" in d["why_not"]

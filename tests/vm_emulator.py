@@ -65,8 +65,22 @@ def emulate_forward(desc, x, w):
     spw = G // T if wb == 0 else 1
     assert x.shape[0] == spw
     state = np.zeros((G, 32), complex)
-    for s in range(spw):
-        state[s * T, 0] = 1.0
+    if desc.get("amplitude"):
+        # x row (first 2^n entries, zero padded), normalised, gathered into the initial layout
+        ibw = desc["initial_bit_of_wire"]
+        for s in range(spw):
+            row = np.zeros(1 << n)
+            kk = min(1 << n, x.shape[1])
+            row[:kk] = x[s, :kk]
+            row /= np.linalg.norm(row)
+            for t in range(T):
+                for jj in range(32):
+                    p = jj | (t << 5)
+                    k = sum(((p >> ibw[w]) & 1) << (n - 1 - w) for w in range(n))
+                    state[s * T + t, jj] = row[k]
+    else:
+        for s in range(spw):
+            state[s * T, 0] = 1.0
     lane = np.arange(G)
     lis = lane % T                       # thread in sample
     samp = lane // T
