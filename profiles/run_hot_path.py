@@ -23,24 +23,24 @@ torch.manual_seed(0)
 x = (2 * torch.rand(B, n, device="cuda") - 1)
 w = 2 * torch.pi * torch.rand(circ.n_weights, device="cuda")
 gy = torch.randn(B, n, device="cuda")
+def timed(fn, reps=5):
+    ts = []
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); out = fn(); e1.record(); torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return min(ts), out
+
 for _ in range(iters):
     y = qris_b200.qnn_forward_raw(circ, x, w)
     gx, gw = qris_b200.qnn_backward_raw(circ, x, w, gy)
-torch.cuda.synchronize()
-ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-ev[0].record(); y = qris_b200.qnn_forward_raw(circ, x, w); ev[1].record()
-gx, gw = qris_b200.qnn_backward_raw(circ, x, w, gy); ev[2].record()
-torch.cuda.synchronize()
-for _ in range(2):
     _, state = qris_b200.qnn_forward_raw(circ, x, w, save_state=True)
     qris_b200.qnn_backward_raw(circ, x, w, gy, state=state)
-del state
 torch.cuda.synchronize()
-ev2 = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-ev2[0].record(); y2, state = qris_b200.qnn_forward_raw(circ, x, w, save_state=True); ev2[1].record()
-gx2, gw2 = qris_b200.qnn_backward_raw(circ, x, w, gy, state=state); ev2[2].record()
-torch.cuda.synchronize()
-print(f"   with saved state: fwd {ev2[0].elapsed_time(ev2[1]):.3f} ms, bwd {ev2[1].elapsed_time(ev2[2]):.3f} ms, "
-      f"max|dgw| vs recompute {float((gw2 - gw).abs().max()):.2e}, max|dgx| {float((gx2 - gx).abs().max()):.2e}")
-print(f"{wl} B={B}: fwd {ev[0].elapsed_time(ev[1]):.3f} ms, bwd {ev[1].elapsed_time(ev[2]):.3f} ms, "
-      f"plan {qris_b200._lib.lib().qnn_circuit_plan(circ.handle(0), B).decode()}")
+f0, _ = timed(lambda: qris_b200.qnn_forward_raw(circ, x, w))
+b0, (gx, gw) = timed(lambda: qris_b200.qnn_backward_raw(circ, x, w, gy))
+f1, (_, state) = timed(lambda: qris_b200.qnn_forward_raw(circ, x, w, save_state=True))
+b1, (gx2, gw2) = timed(lambda: qris_b200.qnn_backward_raw(circ, x, w, gy, state=state))
+plan = qris_b200._lib.lib().qnn_circuit_plan(circ.handle(0), B).decode()
+print(f"{wl} B={B} plan={plan} (best of 5): recompute fwd {f0:.3f} + bwd {b0:.3f} ms | saved-state fwd {f1:.3f} + bwd {b1:.3f} = {f1 + b1:.3f} ms | "
+      f"max|dgw| {float((gw2 - gw).abs().max()):.1e} max|dgx| {float((gx2 - gx).abs().max()):.1e}")

@@ -1,401 +1,39 @@
-// Register-resident statevector VM kernels (program format: qnn_vm.h, compiler: qnn_vm_compile.cpp).
-//
-// One warp carries 1024 amplitudes (32 / 2^tb samples of n = 5 + tb qubits); every lane keeps 32 complex
-// amplitudes in registers.  The kernel is a persistent interpreter: per micro-op one warp-uniform switch
-// selects a fully unrolled body specialised on the register bit(s) it touches, so all state indexing is
-// static and the state never leaves the register file except in EXCHANGE, which re-lays it out through a
-// warp-private 8 KB shared buffer with XOR (GF(2)-linear) addressing that is bank-conflict free on both
-// sides by construction.  FP32 pipe bound; HBM traffic is x, y (and gy, gx) only.
-//
-// Backward = adjoint method: the forward program is re-run to obtain psi, lam = (sum_q gy_q Z_q) psi is
-// seeded, and the program is walked in reverse applying each micro-op's inverse to both vectors while
-// gradients are taken from (lam, psi) pairs:
-//   real rotation    dL/dtheta = Re sum_pairs conj(lam1) psi0 - conj(lam0) psi1
-//   diagonal term    dL/dphi   = sum_p z_bit(p) Im(conj(lam_p) psi_p)
-//   phase on |1>     dL/dphi   = -2 sum_pairs Im(conj(lam1) psi1)        (the two phases of a CU3)
-// Weight-gradient accumulators are reduced over the warp by shuffles, kept per warp in shared memory,
-// summed per CTA in a fixed order and finished by k_vm_finalize: deterministic.
-#include <algorithm>
-#include <cstdio>
-#include <cstdlib>
-
-#include "qnn_vm.h"
+// Host side of the register-resident VM: per-call tables (k_vm_prep), gradient finish (k_vm_finalize),
+// planning and launches.  The kernels themselves live in qnn_vm_kernel.cuh / qnn_vm_g*.cu.
+#include "qnn_vm_kernel.cuh"
 
 namespace vm {
 namespace {
 
-constexpr int NA = kAmps;  // 32
-
-struct VmArgs {
-  const MicroOp* ops; int n_ops;            // including the END marker
-  const Exchange* exchanges; int n_exchanges;
-  const DiagDesc* diags; int n_diags;
-  const float* coef; int n_coef;            // [n_coef][QNN_COEF_STRIDE] (workspace)
-  const float2* big; int n_big;             // [n_big][1024]
-  const float2* small; int n_small;         // [n_small][32]
-  int n, tb, wb, n_inputs, n_acc;           // tb = n - 5 thread bits; wb = warp bits (a group = 2^wb warps)
-  const uint32_t* xbase; int n_xbase;       // per-thread exchange bases
-  unsigned table_bytes;                     // shared-memory bytes of all tables (to place them around the buffers)
-  int cluster;                              // CTAs per sample (cluster geometry), else 0
-  int amplitude;                            // amplitude encoder (GEOM 0 only): x row -> initial state
-  int n_angle;                              // input columns used as angles (0 with the amplitude encoder)
-  int8_t init_bit_of_wire[16];              // initial layout (amplitude encoder)
-  unsigned char* cbuf;                      // cluster geometry: [clusters][2^n * 8] exchange buffers (workspace)
-  float* cred;                              // cluster geometry: [clusters][group warps][48] cross-CTA partials
-  int8_t wire_of_bit[16];                   // final (measurement) layout
-  const float* x; float* y;                 // forward
-  const float* gy; float* gx; float* partial;  // backward; partial [grid][n_acc]
-  float4* state;                            // optional: final psi of every warp-batch (forward writes, backward reads)
-  long long B;
-};
-
-// ---- shared-memory access by 32-bit shared address (XOR addressing needs integer addresses) --------
-__device__ __forceinline__ void sts64(uint32_t addr, float a, float b) {
-  asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
-}
-__device__ __forceinline__ void lds64(uint32_t addr, float& a, float& b) {
-  asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(a), "=f"(b) : "r"(addr) : "memory");
-}
-
-__device__ __forceinline__ void stg64(unsigned char* base, uint32_t off, float a, float b) {
-  __stcg(reinterpret_cast<float2*>(base + off), make_float2(a, b));
-}
-// Plain (L1-allocating) load: only ever issued after the cluster barrier's acquire, which makes the other
-// CTAs' stores visible whatever the cache policy; a reader's neighbouring registers share 32-byte sectors.
-__device__ __forceinline__ void ldg64(const unsigned char* base, uint32_t off, float& a, float& b) {
-  asm volatile("ld.global.v2.f32 {%0, %1}, [%2];" : "=f"(a), "=f"(b) : "l"(base + off) : "memory");
-}
-
-template <int RB>
-__device__ __forceinline__ constexpr int pair_lo(int i) { return ((i >> RB) << (RB + 1)) | (i & ((1 << RB) - 1)); }
-
-// index of the i-th register index (i < 8) with bit RT = 0 and bit RC = 1
-template <int RT, int RC>
-__device__ __forceinline__ constexpr int cpair_lo(int i) {
-  constexpr int lo = RT < RC ? RT : RC, hi = RT < RC ? RC : RT;
-  int v = ((i >> lo) << (lo + 1)) | (i & ((1 << lo) - 1));
-  v = ((v >> hi) << (hi + 1)) | (v & ((1 << hi) - 1));
-  return v | (1 << RC);
-}
-
-// ---- gate bodies ---------------------------------------------------------------------------------
-// The state is kept as (re, im) register pairs and all arithmetic uses Blackwell's packed FP32x2
-// instructions (FFMA2 / FMUL2 / FADD2, sm_100+): one issue slot per two FMAs.  Scalar three-register
-// FFMAs issue at only ~2/3 rate on this part (register-bank read ports; profiles/experiments/fma_rate.cu),
-// so the packed form is what lets the FMA pipe, not the issue port, be the limit.
-__device__ __forceinline__ float2 mul2(float s, float2 a) { return __fmul2_rn(make_float2(s, s), a); }
-__device__ __forceinline__ float2 fma2(float s, float2 a, float2 c) { return __ffma2_rn(make_float2(s, s), a, c); }
-__device__ __forceinline__ float2 swp(float2 a) { return make_float2(a.y, a.x); }
-
-// Real rotation [[c,-s],[s,c]] (c,s = cos,sin(phi)) as three in-place shears
-//   a0 += al*a1;  a1 += be*a0;  a0 += al*a1       al = -tan(phi/2), be = sin(phi)
-// 3 packed FMAs per amplitude pair, no temporaries; the inverse uses (-al, -be).  phi is range-reduced to
-// [-pi/2, pi/2] when the coefficients are made, so |al| <= 0.415.
-template <int RB>
-__device__ __forceinline__ void rot(float2 (&st)[NA], float al, float be) {
-#pragma unroll
-  for (int i = 0; i < NA / 2; ++i) {
-    const int j0 = pair_lo<RB>(i), j1 = j0 | (1 << RB);
-    st[j0] = fma2(al, st[j1], st[j0]);
-    st[j1] = fma2(be, st[j0], st[j1]);
-    st[j0] = fma2(al, st[j1], st[j0]);
-  }
-}
-// Re sum conj(l1) p0 - conj(l0) p1  (gradient of a rotation angle, from the AFTER vectors)
-__device__ __forceinline__ void rot_grad_acc(float2& v0, float2& v1, float2 p0, float2 p1, float2 l0, float2 l1) {
-  v0 = __ffma2_rn(l1, p0, v0);
-  v1 = __ffma2_rn(l0, p1, v1);
-}
-template <int RB>
-__device__ __forceinline__ float rot_grad(const float2 (&ps)[NA], const float2 (&ls)[NA]) {
-  const float2 z = make_float2(0.f, 0.f);
-  float2 v0[4] = {z, z, z, z}, v1[4] = {z, z, z, z};   // four independent chains: the FMA latency is exposed otherwise
-#pragma unroll
-  for (int i = 0; i < NA / 2; ++i) {
-    const int j0 = pair_lo<RB>(i), j1 = j0 | (1 << RB);
-    rot_grad_acc(v0[i & 3], v1[i & 3], ps[j0], ps[j1], ls[j0], ls[j1]);
-  }
-  const float2 a = __fadd2_rn(__fadd2_rn(v0[0], v0[1]), __fadd2_rn(v0[2], v0[3]));
-  const float2 b = __fadd2_rn(__fadd2_rn(v1[0], v1[1]), __fadd2_rn(v1[2], v1[3]));
-  return (a.x + a.y) - (b.x + b.y);
-}
-
-// a <- e * a for a unit complex e = (er, ei), in place: er*a + (-ei, ei) (.) swap(a)
-__device__ __forceinline__ float2 cmul(float er, float2 ei2, float2 a) { return __ffma2_rn(ei2, swp(a), mul2(er, a)); }
-
-// Controlled U3 on one control=1 pair: diag(1, e^{i phi}) * m0 R(phi') * diag(1, e^{i lambda}); the sign
-// m0 = +-1 of the range reduction is folded into the first phase (a1) and one multiply (a0).
-struct Cu3 {
-  float al, be, m0, elr, epr;
-  float2 eli, epi;     // (-im, +im) of m0*e^{i lambda} and e^{i phi}
-};
-__device__ __forceinline__ Cu3 make_cu3(float4 a, float4 b, bool inverse) {
-  Cu3 g;
-  g.m0 = a.z;
-  if (!inverse) {
-    g.al = a.x; g.be = a.y; g.elr = a.z * b.x; g.eli = make_float2(-a.z * b.y, a.z * b.y);
-    g.epr = b.z; g.epi = make_float2(-b.w, b.w);
-  } else {   // conjugate phases, opposite shears
-    g.al = -a.x; g.be = -a.y; g.elr = a.z * b.x; g.eli = make_float2(a.z * b.y, -a.z * b.y);
-    g.epr = b.z; g.epi = make_float2(b.w, -b.w);
-  }
-  return g;
-}
-__device__ __forceinline__ void cu3_pair(const Cu3& g, float2& a0, float2& a1) {
-  a1 = cmul(g.elr, g.eli, a1);
-  a0 = mul2(g.m0, a0);
-  a0 = fma2(g.al, a1, a0);
-  a1 = fma2(g.be, a0, a1);
-  a0 = fma2(g.al, a1, a0);
-  a1 = cmul(g.epr, g.epi, a1);
-}
-__device__ __forceinline__ Cu3 load_cu3(const float* c, bool inverse) {
-  return make_cu3(*reinterpret_cast<const float4*>(c), *reinterpret_cast<const float4*>(c + 4), inverse);
-}
-// Reverse step on one pair, for psi (p) and lam (l) together, g = load_cu3(.., inverse=true).
-// Accumulates (as packed pairs, finished by the caller): q_phi, v_theta0/1, q_lambda.
-struct Cu3Acc { float2 qp, v0, v1, ql; };
-__device__ __forceinline__ void cu3_pair_bwd(const Cu3& g, float2& p0, float2& p1, float2& l0, float2& l1, Cu3Acc& A) {
-  A.qp = __ffma2_rn(l1, swp(p1), A.qp);           // (l.re p.im, l.im p.re): Im(conj(l1) p1) = x - y
-  p1 = cmul(g.epr, g.epi, p1); l1 = cmul(g.epr, g.epi, l1);
-  rot_grad_acc(A.v0, A.v1, p0, p1, l0, l1);
-  p0 = fma2(g.al, p1, p0); p1 = fma2(g.be, p0, p1); p0 = fma2(g.al, p1, p0);
-  l0 = fma2(g.al, l1, l0); l1 = fma2(g.be, l0, l1); l0 = fma2(g.al, l1, l0);
-  p0 = mul2(g.m0, p0); l0 = mul2(g.m0, l0);
-  A.ql = __ffma2_rn(l1, swp(p1), A.ql);
-  p1 = cmul(g.elr, g.eli, p1); l1 = cmul(g.elr, g.eli, l1);
-}
-template <int RT, int RC>
-__device__ __forceinline__ void cu3_loc(float2 (&st)[NA], const Cu3& g) {
-#pragma unroll
-  for (int i = 0; i < NA / 4; ++i) {
-    const int j0 = cpair_lo<RT, RC>(i), j1 = j0 | (1 << RT);
-    cu3_pair(g, st[j0], st[j1]);
-  }
-}
-template <int RB>
-__device__ __forceinline__ void cu3_all(float2 (&st)[NA], const Cu3& g) {
-#pragma unroll
-  for (int i = 0; i < NA / 2; ++i) {
-    const int j0 = pair_lo<RB>(i), j1 = j0 | (1 << RB);
-    cu3_pair(g, st[j0], st[j1]);
-  }
-}
-template <int RT, int RC>
-__device__ __forceinline__ void cu3_loc_bwd(float2 (&ps)[NA], float2 (&ls)[NA], const Cu3& g, Cu3Acc& A) {
-#pragma unroll
-  for (int i = 0; i < NA / 4; ++i) {
-    const int j0 = cpair_lo<RT, RC>(i), j1 = j0 | (1 << RT);
-    cu3_pair_bwd(g, ps[j0], ps[j1], ls[j0], ls[j1], A);
-  }
-}
-template <int RB>
-__device__ __forceinline__ void cu3_all_bwd(float2 (&ps)[NA], float2 (&ls)[NA], const Cu3& g, Cu3Acc& A) {
-#pragma unroll
-  for (int i = 0; i < NA / 2; ++i) {
-    const int j0 = pair_lo<RB>(i), j1 = j0 | (1 << RB);
-    cu3_pair_bwd(g, ps[j0], ps[j1], ls[j0], ls[j1], A);
-  }
-}
-
-// ---- sums over the 32 register amplitudes: total and, per register bit r, the signed sum -------------
-// S[r] = sum_j (-1)^{j_r} v_j with a shared tree (61 packed adds); v_j are pairs, reduced per half.
-template <typename F>
-__device__ __forceinline__ void signed_sums2(F f, float2& total, float2 (&S)[kR]) {
-  const float2 z = make_float2(0.f, 0.f);
-  float2 a[16], o0 = z;
-#pragma unroll
-  for (int i = 0; i < 16; ++i) { const float2 e = f(2 * i), o = f(2 * i + 1); a[i] = __fadd2_rn(e, o); o0 = __fadd2_rn(o0, o); }
-  float2 b[8], o1 = z;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) { b[i] = __fadd2_rn(a[2 * i], a[2 * i + 1]); o1 = __fadd2_rn(o1, a[2 * i + 1]); }
-  float2 c[4], o2 = z;
-#pragma unroll
-  for (int i = 0; i < 4; ++i) { c[i] = __fadd2_rn(b[2 * i], b[2 * i + 1]); o2 = __fadd2_rn(o2, b[2 * i + 1]); }
-  const float2 d0 = __fadd2_rn(c[0], c[1]), d1 = __fadd2_rn(c[2], c[3]);
-  const float2 o3 = __fadd2_rn(c[1], c[3]), o4 = d1;
-  total = __fadd2_rn(d0, d1);
-  S[0] = fma2(-2.f, o0, total); S[1] = fma2(-2.f, o1, total); S[2] = fma2(-2.f, o2, total);
-  S[3] = fma2(-2.f, o3, total); S[4] = fma2(-2.f, o4, total);
-}
-
-__device__ __forceinline__ float warp_sum(float v) {   // over all 32 lanes
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
-}
-__device__ __forceinline__ float sample_sum(float v, int tb) {   // over the 2^tb lanes of one sample
-  for (int b = 0; b < tb; ++b) v += __shfl_xor_sync(0xffffffffu, v, 1 << b);
-  return v;
-}
-// 16 values summed over the warp with the halving butterfly (8+4+2+1+1 = 16 shuffles, depth 5):
-// afterwards lane l holds component l >> 1, fully reduced.
-__device__ __forceinline__ float warp_sum16(const float (&t)[16], int lane) {
-  float k8[8], k4[4], k2[2];
-  {
-    const bool up = lane & 16;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) k8[i] = (up ? t[8 + i] : t[i]) + __shfl_xor_sync(0xffffffffu, up ? t[i] : t[8 + i], 16);
-  }
-  {
-    const bool up = lane & 8;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) k4[i] = (up ? k8[4 + i] : k8[i]) + __shfl_xor_sync(0xffffffffu, up ? k8[i] : k8[4 + i], 8);
-  }
-  {
-    const bool up = lane & 4;
-#pragma unroll
-    for (int i = 0; i < 2; ++i) k2[i] = (up ? k4[2 + i] : k4[i]) + __shfl_xor_sync(0xffffffffu, up ? k4[i] : k4[2 + i], 4);
-  }
-  float k;
-  {
-    const bool up = lane & 2;
-    k = (up ? k2[1] : k2[0]) + __shfl_xor_sync(0xffffffffu, up ? k2[0] : k2[1], 2);
-  }
-  k += __shfl_xor_sync(0xffffffffu, k, 1);
-  return k;
-}
-
-// 4 values summed over the warp with the halving butterfly: afterwards lane l holds component
-// 2*bit4 + bit3 of l, fully reduced (9 shuffles instead of 20).
-__device__ __forceinline__ float warp_sum4(float t0, float t1, float t2, float t3, int lane) {
-  float k0, k1;
-  {
-    const bool up = lane & 16;
-    k0 = (up ? t2 : t0) + __shfl_xor_sync(0xffffffffu, up ? t0 : t2, 16);
-    k1 = (up ? t3 : t1) + __shfl_xor_sync(0xffffffffu, up ? t1 : t3, 16);
-  }
-  float k;
-  {
-    const bool up = lane & 8;
-    k = (up ? k1 : k0) + __shfl_xor_sync(0xffffffffu, up ? k0 : k1, 8);
-  }
-  k += __shfl_xor_sync(0xffffffffu, k, 4);
-  k += __shfl_xor_sync(0xffffffffu, k, 2);
-  k += __shfl_xor_sync(0xffffffffu, k, 1);
-  return k;
-}
-
-// ---- exchange ---------------------------------------------------------------------------------------
-// wa / ra: this thread's write / read base (buffer address | per-thread offset); `sync` is the barrier
-// of the group that shares the buffer (a warp for n <= 10, 2^wb warps above).
-template <typename Sync>
-__device__ __forceinline__ void exchange(float2 (&st)[NA], uint32_t wa, uint32_t ra, const uint32_t* woff,
-                                         const uint32_t* roff, Sync sync) {
-  sync();
-#pragma unroll
-  for (int q = 0; q < NA / 4; ++q) {
-    const uint4 o = *reinterpret_cast<const uint4*>(woff + 4 * q);
-    sts64(wa ^ o.x, st[4 * q + 0].x, st[4 * q + 0].y);
-    sts64(wa ^ o.y, st[4 * q + 1].x, st[4 * q + 1].y);
-    sts64(wa ^ o.z, st[4 * q + 2].x, st[4 * q + 2].y);
-    sts64(wa ^ o.w, st[4 * q + 3].x, st[4 * q + 3].y);
-  }
-  sync();
-#pragma unroll
-  for (int q = 0; q < NA / 4; ++q) {
-    const uint4 o = *reinterpret_cast<const uint4*>(roff + 4 * q);
-    lds64(ra ^ o.x, st[4 * q + 0].x, st[4 * q + 0].y);
-    lds64(ra ^ o.y, st[4 * q + 1].x, st[4 * q + 1].y);
-    lds64(ra ^ o.z, st[4 * q + 2].x, st[4 * q + 2].y);
-    lds64(ra ^ o.w, st[4 * q + 3].x, st[4 * q + 3].y);
-  }
-}
-
-// Cluster geometry (n >= 14): the buffers are slices of the workspace (L2), accessed around L1.  Buffer
-// sets alternate from one exchange to the next, so ONE cluster barrier per exchange suffices: a set is
-// written again only after every thread has passed the barrier of the exchange in between, i.e. after
-// all reads of it have completed.  TWO: psi and lam travel together (backward), sharing that barrier.
-template <bool TWO, typename Sync>
-__device__ __forceinline__ void exchange_global(float2 (&st)[NA], float2 (&st2)[NA], unsigned char* buf, unsigned char* buf2,
-                                                uint32_t wa, uint32_t ra, const uint32_t* woff, const uint32_t* roff, Sync sync) {
-#pragma unroll
-  for (int q = 0; q < NA / 4; ++q) {
-    const uint4 o = *reinterpret_cast<const uint4*>(woff + 4 * q);
-    stg64(buf, wa ^ o.x, st[4 * q + 0].x, st[4 * q + 0].y);
-    stg64(buf, wa ^ o.y, st[4 * q + 1].x, st[4 * q + 1].y);
-    stg64(buf, wa ^ o.z, st[4 * q + 2].x, st[4 * q + 2].y);
-    stg64(buf, wa ^ o.w, st[4 * q + 3].x, st[4 * q + 3].y);
-    if (TWO) {
-      stg64(buf2, wa ^ o.x, st2[4 * q + 0].x, st2[4 * q + 0].y);
-      stg64(buf2, wa ^ o.y, st2[4 * q + 1].x, st2[4 * q + 1].y);
-      stg64(buf2, wa ^ o.z, st2[4 * q + 2].x, st2[4 * q + 2].y);
-      stg64(buf2, wa ^ o.w, st2[4 * q + 3].x, st2[4 * q + 3].y);
-    }
-  }
-  sync();
-#pragma unroll
-  for (int q = 0; q < NA / 4; ++q) {
-    const uint4 o = *reinterpret_cast<const uint4*>(roff + 4 * q);
-    ldg64(buf, ra ^ o.x, st[4 * q + 0].x, st[4 * q + 0].y);
-    ldg64(buf, ra ^ o.y, st[4 * q + 1].x, st[4 * q + 1].y);
-    ldg64(buf, ra ^ o.z, st[4 * q + 2].x, st[4 * q + 2].y);
-    ldg64(buf, ra ^ o.w, st[4 * q + 3].x, st[4 * q + 3].y);
-    if (TWO) {
-      ldg64(buf2, ra ^ o.x, st2[4 * q + 0].x, st2[4 * q + 0].y);
-      ldg64(buf2, ra ^ o.y, st2[4 * q + 1].x, st2[4 * q + 1].y);
-      ldg64(buf2, ra ^ o.z, st2[4 * q + 2].x, st2[4 * q + 2].y);
-      ldg64(buf2, ra ^ o.w, st2[4 * q + 3].x, st2[4 * q + 3].y);
-    }
-  }
-}
-
-// multiply by a diagonal (optionally its conjugate): big table [j][lane] or register-only table [j].
-// d*a = d.re * a + (-d.im, d.im) (.) swap(a); one table load serves psi and lam in the backward pass.
-template <bool CONJ, bool TWO>
-__device__ __forceinline__ void diag_mul(float2 (&st)[NA], float2 (&st2)[NA], const float2* tbl, int stride, int lane_off) {
-#pragma unroll
-  for (int j = 0; j < NA; ++j) {
-    const float2 d = tbl[j * stride + lane_off];
-    const float2 di = CONJ ? make_float2(d.y, -d.y) : make_float2(-d.y, d.y);
-    st[j] = __ffma2_rn(di, swp(st[j]), mul2(d.x, st[j]));
-    if (TWO) st2[j] = __ffma2_rn(di, swp(st2[j]), mul2(d.x, st2[j]));
-  }
-}
-
-// Shear coefficients of RY(x) = R(x/2) for a per-sample angle: (al, be) = (-tan(phi'/2), sin phi') with
-// phi' = x/2 reduced to [-pi/2, pi/2]; the dropped sign (-1)^k is a global phase of the sample's state.
-__device__ __forceinline__ float2 rot_coef_x(float xv) {
-  float phi = 0.5f * xv;
-  phi = fmaf(-3.14159265358979323846f, rintf(phi * 0.318309886183790672f), phi);
-  float sh, ch;
-  sincosf(0.5f * phi, &sh, &ch);
-  return make_float2(-sh / ch, 2.f * sh * ch);
-}
-
-struct Smem {
-  MicroOp* ops;
-  Exchange* exchanges;
-  uint32_t* xbase;
-  DiagDesc* diags;
-  float* coef;        // [n_coef][8]
-  const float2* big;  // [n_big][32 * G]: shared memory for n <= 10, the workspace (L2) above
-  float2* small;      // [n_small][32]
-  float* wacc;        // [warps][n_acc]        (backward)
-  float* gxacc;       // [warps][spw * n_inputs]
-  float2* xcoef;      // [warps][spw * n_inputs]: shear coefficients of RY(x[b, col]), made once per batch
-  float* red;         // [groups][group warps][16]: cross-warp measurement partials (n > 10)
-  uint32_t xbuf;      // shared address of this group's exchange buffer (8 KB per warp, aligned to its size)
-};
-
-size_t table_bytes(const Program& p, int n_inputs, int warps, bool bwd, bool cluster) {
-  auto up = [](size_t v) { return (v + 15) & ~size_t(15); };
+// Layout of the shared-memory tables (byte offsets from their base); `total` is what they need.
+struct TableLayout { unsigned ops, exch, xbase, diags, coef, big, small, xcoef, red, wacc, gxacc, total; };
+TableLayout table_layout(const Program& p, int n_inputs, int warps, bool bwd, bool cluster) {
   const int G = 32 << p.wb, spw = p.wb ? 1 : (32 >> p.tb);
-  size_t b = 0;
-  b += up(p.ops.size() * sizeof(MicroOp));
-  b += up(p.exchanges.size() * sizeof(Exchange));
-  if (!cluster) b += up(p.xbase.size() * sizeof(uint32_t));
-  b += up(p.diags.size() * sizeof(DiagDesc));
-  b += up(p.coef_ops.size() * 8 * sizeof(float));
-  if (p.wb == 0) b += up((size_t)p.n_big_tables * 32 * G * sizeof(float2));
-  b += up((size_t)p.n_small_tables * 32 * sizeof(float2));
-  b += up((size_t)warps * spw * std::max(n_inputs, 1) * sizeof(float2));
-  b += up((size_t)warps * 16 * sizeof(float));
+  unsigned at = 0;
+  auto take = [&](size_t bytes) { const unsigned r = at; at += (unsigned)((bytes + 15) & ~size_t(15)); return r; };
+  // diagonal tables are read as one 256-byte row per warp instruction: a row that straddles 128-byte lines
+  // costs an extra shared-memory wavefront per read (dynamic shared memory starts 1 KB-aligned)
+  auto align256 = [&]() { at = (at + 255u) & ~255u; };
+  TableLayout t{};
+  t.ops = take(p.ops.size() * sizeof(MicroOp));
+  t.exch = take(p.exchanges.size() * sizeof(Exchange));
+  t.xbase = cluster ? 0u : take(p.xbase.size() * sizeof(uint32_t));
+  t.diags = take(p.diags.size() * sizeof(DiagDesc));
+  t.coef = take(p.coef_ops.size() * 8 * sizeof(float));
+  align256();
+  t.big = p.wb == 0 ? take((size_t)p.n_big_tables * 32 * G * sizeof(float2)) : 0u;
+  t.small = take((size_t)p.n_small_tables * 32 * sizeof(float2));
+  t.xcoef = take((size_t)warps * spw * std::max(n_inputs, 1) * sizeof(float2));
+  t.red = take((size_t)warps * 16 * sizeof(float));
   if (bwd) {
-    b += up((size_t)warps * std::max(p.n_acc, 1) * sizeof(float));
-    b += up((size_t)warps * spw * std::max(n_inputs, 1) * sizeof(float));
+    t.wacc = take((size_t)warps * std::max(p.n_acc, 1) * sizeof(float));
+    t.gxacc = take((size_t)warps * spw * std::max(n_inputs, 1) * sizeof(float));
   }
-  return b;
+  t.total = at;
+  return t;
+}
+size_t table_bytes(const Program& p, int n_inputs, int warps, bool bwd, bool cluster) {
+  return table_layout(p, n_inputs, warps, bwd, cluster).total;
 }
 // exchange buffers (8 KB per warp, each group's aligned to its size) + worst-case alignment gap + tables;
 // the cluster geometry keeps its exchange buffer in the workspace
@@ -403,450 +41,6 @@ size_t smem_bytes(const Program& p, int n_inputs, int warps, bool bwd, bool clus
   if (cluster) return table_bytes(p, n_inputs, warps, bwd, true) + 64;
   const size_t group_buf = (size_t)8192 << p.wb;
   return group_buf + (size_t)warps * 8192 + table_bytes(p, n_inputs, warps, bwd, false) + 64;
-}
-
-// GEOM 0: a warp carries whole samples (n <= 10): constant strides, __syncwarp barriers.
-// GEOM 1: a sample spans 2^wb warps of one CTA (n = 11..13): shared exchange buffer, named barriers.
-// GEOM 2: a sample spans a thread-block cluster (n = 14..16): exchange buffer in L2, cluster barriers,
-//         per-thread bases and cross-CTA partial sums in global memory.
-template <bool BWD, int THREADS, int MINB, bool STATE, int GEOM>
-__global__ void __launch_bounds__(THREADS, MINB) k_vm(const VmArgs a) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int WARPS = blockDim.x >> 5;     // THREADS is the launch bound; fewer warps may be launched
-  constexpr bool MW = GEOM >= 1, CL = GEOM == 2;
-  const int tb = a.tb, wbits = MW ? a.wb : 0;
-  const int gwarps = 1 << wbits, G = 32 << wbits;          // warps / threads per group (one sample for n >= 10)
-  unsigned crank = 0, cid = blockIdx.x, ncl = gridDim.x;   // cluster rank / id / count (GEOM 2)
-  if constexpr (CL) {
-    asm("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
-    cid = blockIdx.x / (unsigned)a.cluster; ncl = gridDim.x / (unsigned)a.cluster;
-  }
-  const int gw = CL ? (int)crank * WARPS + warp : (warp & (gwarps - 1));   // warp in group
-  const int grp = CL ? 0 : (warp >> wbits), groups = CL ? 1 : (WARPS >> wbits);
-  const int spw = wbits ? 1 : (32 >> tb);                  // samples per warp (n <= 10)
-  const int tig = (gw << 5) | lane;                        // thread in group
-  const int tis = wbits ? tig : (lane & ((1 << tb) - 1));  // thread in sample: the sample's thread bits
-  const int siw = wbits ? 0 : (lane >> tb);                // sample in warp
-  const int lbits = tb < 5 ? tb : 5;                       // thread bits that are lanes of this warp
-
-  // ---- carve shared memory: group exchange buffers (aligned to their size); tables go into the
-  //      alignment gap below them when they fit, else behind them ------------------------------------
-  Smem S;
-  {
-    const uint32_t s0 = (uint32_t)__cvta_generic_to_shared(smem_raw);
-    const uint32_t gbuf = CL ? 16u : (8192u << wbits);
-    const uint32_t xb = (s0 + gbuf - 1u) & ~(gbuf - 1u);
-    S.xbuf = xb + (uint32_t)grp * gbuf;
-    const size_t tables = a.table_bytes;
-    unsigned char* p = CL ? smem_raw : ((xb - s0 >= tables) ? smem_raw : smem_raw + (xb - s0) + (size_t)WARPS * 8192);
-    auto take = [&](size_t bytes) { unsigned char* r = p; p += (bytes + 15) & ~size_t(15); return r; };
-    S.ops = reinterpret_cast<MicroOp*>(take((size_t)a.n_ops * sizeof(MicroOp)));
-    S.exchanges = reinterpret_cast<Exchange*>(take((size_t)a.n_exchanges * sizeof(Exchange)));
-    S.xbase = CL ? const_cast<uint32_t*>(a.xbase) : reinterpret_cast<uint32_t*>(take((size_t)a.n_xbase * sizeof(uint32_t)));
-    S.diags = reinterpret_cast<DiagDesc*>(take((size_t)a.n_diags * sizeof(DiagDesc)));
-    S.coef = reinterpret_cast<float*>(take((size_t)a.n_coef * 8 * sizeof(float)));
-    float2* sbig = wbits == 0 ? reinterpret_cast<float2*>(take((size_t)a.n_big * 32 * G * sizeof(float2))) : nullptr;
-    S.big = wbits == 0 ? sbig : a.big;
-    S.small = reinterpret_cast<float2*>(take((size_t)a.n_small * 32 * sizeof(float2)));
-    S.xcoef = reinterpret_cast<float2*>(take((size_t)WARPS * spw * max(a.n_angle, 1) * sizeof(float2)));
-    S.red = reinterpret_cast<float*>(take((size_t)WARPS * 16 * sizeof(float)));
-    if (BWD) {
-      S.wacc = reinterpret_cast<float*>(take((size_t)WARPS * max(a.n_acc, 1) * sizeof(float)));
-      S.gxacc = reinterpret_cast<float*>(take((size_t)WARPS * spw * max(a.n_angle, 1) * sizeof(float)));
-    }
-    const int tid = threadIdx.x;
-    const uint32_t* src; uint32_t* dst; int words;
-    src = reinterpret_cast<const uint32_t*>(a.ops); dst = reinterpret_cast<uint32_t*>(S.ops); words = a.n_ops * (int)(sizeof(MicroOp) / 4);
-    for (int i = tid; i < words; i += blockDim.x) dst[i] = src[i];
-    src = reinterpret_cast<const uint32_t*>(a.exchanges); dst = reinterpret_cast<uint32_t*>(S.exchanges); words = a.n_exchanges * (int)(sizeof(Exchange) / 4);
-    for (int i = tid; i < words; i += blockDim.x) dst[i] = src[i];
-    if (!CL) for (int i = tid; i < a.n_xbase; i += blockDim.x) S.xbase[i] = a.xbase[i];
-    src = reinterpret_cast<const uint32_t*>(a.diags); dst = reinterpret_cast<uint32_t*>(S.diags); words = a.n_diags * (int)(sizeof(DiagDesc) / 4);
-    for (int i = tid; i < words; i += blockDim.x) dst[i] = src[i];
-    for (int i = tid; i < a.n_coef * 8; i += blockDim.x) S.coef[i] = a.coef[(size_t)(i >> 3) * QNN_COEF_STRIDE + (i & 7)];
-    if (wbits == 0) for (int i = tid; i < a.n_big * 32 * G; i += blockDim.x) sbig[i] = a.big[i];
-    for (int i = tid; i < a.n_small * 32; i += blockDim.x) S.small[i] = a.small[i];
-    if (BWD) {
-      for (int i = tid; i < WARPS * max(a.n_acc, 1); i += blockDim.x) S.wacc[i] = 0.f;
-      for (int i = tid; i < WARPS * spw * max(a.n_angle, 1); i += blockDim.x) S.gxacc[i] = 0.f;
-    }
-  }
-  __syncthreads();
-  float* const wacc = BWD ? S.wacc + (size_t)warp * max(a.n_acc, 1) : nullptr;
-  float* const gxacc = BWD ? S.gxacc + (size_t)warp * spw * max(a.n_angle, 1) : nullptr;
-  float* const red = S.red + (size_t)warp * 16;
-  // barrier over the threads that share one exchange buffer
-  auto gsync = [&]() {
-    if constexpr (!MW) __syncwarp();
-    else if constexpr (!CL) asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "r"(G) : "memory");
-    else {   // every thread of every CTA of the cluster; release/acquire orders the global exchange traffic
-      asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-    }
-  };
-  // cluster geometry: four exchange buffers per cluster (two alternating sets of {psi, lam})
-  unsigned char* const cbuf = CL ? a.cbuf + ((size_t)cid << (a.n + 5)) : nullptr;
-  const size_t cbuf_one = (size_t)1 << (a.n + 3);
-  unsigned xpar = 0;
-  float* const cred = CL ? a.cred + (size_t)cid * gwarps * 48 : nullptr;
-
-  float2* const xcoef = S.xcoef + (size_t)warp * spw * max(a.n_angle, 1);
-  const int n_ang = a.n_angle;
-  // amplitude encoder: logical index (wire 0 = most significant bit) of this thread's register j is klog_t | klog_j(j)
-  auto klog = [&](unsigned p) { unsigned k = 0; for (int w = 0; w < a.n; ++w) k |= ((p >> a.init_bit_of_wire[w]) & 1u) << (a.n - 1 - w); return k; };
-  const unsigned klog_t = (GEOM == 0 && a.amplitude) ? klog((unsigned)tis << kR) : 0u;
-  float2 ps[NA];
-  const long long n_batches = (a.B + spw - 1) / spw;
-  for (long long wb = CL ? (long long)cid : (long long)blockIdx.x * groups + grp; wb < n_batches;
-       wb += CL ? (long long)ncl : (long long)gridDim.x * groups) {
-    const long long bs = wb * spw + siw;
-    const bool active = bs < a.B;
-    gsync();   // nothing of the previous batch (scratch, exchange buffer) is still being read
-
-    // shear coefficients of the per-sample rotations RY(x[b, col]): each (sample, column) once per batch
-    for (int i = lane; i < spw * n_ang; i += 32) {
-      const long long bb = wb * spw + i / n_ang;
-      xcoef[i] = rot_coef_x(bb < a.B ? a.x[(size_t)bb * a.n_inputs + (i % n_ang)] : 0.f);
-    }
-    __syncwarp();
-    const float2* const xc = xcoef + siw * n_ang;
-
-    // Saved final state: [batch][j / 2][lane] float4 = amplitudes (2 * (j/2), 2 * (j/2) + 1) of that lane;
-    // a warp reads or writes 512 contiguous bytes per instruction.
-    float4* const st_rows = STATE ? a.state + (size_t)wb * (NA / 2) * G + tig : nullptr;
-    if constexpr (BWD && STATE) {
-#pragma unroll
-      for (int q = 0; q < NA / 2; ++q) {
-        const float4 v = __ldcs(st_rows + (size_t)q * G);
-        ps[2 * q] = make_float2(v.x, v.y); ps[2 * q + 1] = make_float2(v.z, v.w);
-      }
-    } else {
-#pragma unroll
-    for (int j = 0; j < NA; ++j) ps[j] = make_float2(0.f, 0.f);
-    if (GEOM == 0 && a.amplitude) {
-      // |psi> = x / |x| (first 2^n entries of the row, zero padded), gathered into the initial layout
-      const float* xr = a.x + (size_t)(active ? bs : 0) * a.n_inputs;
-      float ss = 0.f;
-#pragma unroll
-      for (int j = 0; j < NA; ++j) {
-        const unsigned k = klog_t | klog((unsigned)j);
-        const float v = (active && (int)k < a.n_inputs) ? xr[k] : 0.f;
-        ps[j].x = v;
-        ss = fmaf(v, v, ss);
-      }
-      const float inv = rsqrtf(sample_sum(ss, lbits));
-#pragma unroll
-      for (int j = 0; j < NA; ++j) ps[j].x *= inv;
-    } else {
-      ps[0].x = tis == 0 ? 1.f : 0.f;
-    }
-
-    // ================= forward program =================
-    // One jump per micro-op (handler id = kind and register bits); the next op and its coefficient row
-    // are fetched while the current body runs, so the dispatch latency overlaps with arithmetic.
-    {
-      MicroOp op = S.ops[0];
-      float4 cfa = *reinterpret_cast<const float4*>(S.coef + op.pad1 * 8);
-      for (int pc = 0; op.pad0 != H_END; ++pc) {
-        const MicroOp next = S.ops[pc + 1];
-        const float4 ncfa = *reinterpret_cast<const float4*>(S.coef + next.pad1 * 8);
-        switch (op.pad0) {
-#define H_CASE_ROT(RB) case H_ROT + RB: rot<RB>(ps, cfa.x, cfa.y); break;
-          H_CASE_ROT(0) H_CASE_ROT(1) H_CASE_ROT(2) H_CASE_ROT(3) H_CASE_ROT(4)
-#undef H_CASE_ROT
-#define H_CASE_ROTX(RB) case H_ROTX + RB: { const float2 ab = xc[op.idx]; rot<RB>(ps, ab.x, ab.y); } break;
-          H_CASE_ROTX(0) H_CASE_ROTX(1) H_CASE_ROTX(2) H_CASE_ROTX(3) H_CASE_ROTX(4)
-#undef H_CASE_ROTX
-#define H_CASE_CU3L(RT, RC) case H_CU3L + RT * 4 + (RC < RT ? RC : RC - 1): { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_loc<RT, RC>(ps, g); } break;
-          H_CASE_CU3L(0, 1) H_CASE_CU3L(0, 2) H_CASE_CU3L(0, 3) H_CASE_CU3L(0, 4)
-          H_CASE_CU3L(1, 0) H_CASE_CU3L(1, 2) H_CASE_CU3L(1, 3) H_CASE_CU3L(1, 4)
-          H_CASE_CU3L(2, 0) H_CASE_CU3L(2, 1) H_CASE_CU3L(2, 3) H_CASE_CU3L(2, 4)
-          H_CASE_CU3L(3, 0) H_CASE_CU3L(3, 1) H_CASE_CU3L(3, 2) H_CASE_CU3L(3, 4)
-          H_CASE_CU3L(4, 0) H_CASE_CU3L(4, 1) H_CASE_CU3L(4, 2) H_CASE_CU3L(4, 3)
-#undef H_CASE_CU3L
-#define H_CASE_CU3P(RB) case H_CU3P + RB: if (__popc(tis & op.aux) & 1) { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_all<RB>(ps, g); } break;
-          H_CASE_CU3P(0) H_CASE_CU3P(1) H_CASE_CU3P(2) H_CASE_CU3P(3) H_CASE_CU3P(4)
-#undef H_CASE_CU3P
-          case H_ROT5: {
-            float2 ab[5];
-#pragma unroll
-            for (int k = 0; k < 5; ++k) ab[k] = *reinterpret_cast<const float2*>(S.coef + (op.idx + ((op.aux >> (3 * k)) & 7)) * 8);
-            rot<0>(ps, ab[0].x, ab[0].y); rot<1>(ps, ab[1].x, ab[1].y); rot<2>(ps, ab[2].x, ab[2].y);
-            rot<3>(ps, ab[3].x, ab[3].y); rot<4>(ps, ab[4].x, ab[4].y);
-          } break;
-          case H_ROTX5: {
-            float2 ab[5];
-#pragma unroll
-            for (int k = 0; k < 5; ++k) ab[k] = xc[(op.idx >> (5 * k)) & 31];
-            rot<0>(ps, ab[0].x, ab[0].y); rot<1>(ps, ab[1].x, ab[1].y); rot<2>(ps, ab[2].x, ab[2].y);
-            rot<3>(ps, ab[3].x, ab[3].y); rot<4>(ps, ab[4].x, ab[4].y);
-          } break;
-          case H_CHAIN: {
-            { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_loc<1, 0>(ps, g); }
-            { const Cu3 g = load_cu3(S.coef + (op.idx + 1) * 8, false); cu3_loc<2, 1>(ps, g); }
-            { const Cu3 g = load_cu3(S.coef + (op.idx + 2) * 8, false); cu3_loc<3, 2>(ps, g); }
-            { const Cu3 g = load_cu3(S.coef + (op.idx + 3) * 8, false); cu3_loc<4, 3>(ps, g); }
-          } break;
-          case H_DIAG: diag_mul<false, false>(ps, ps, S.big + (size_t)op.idx * 32 * G, G, tig); break;
-          case H_DIAGR: diag_mul<false, false>(ps, ps, S.small + op.idx * 32, 1, 0); break;
-          case H_XCHG: {
-            const Exchange* X = S.exchanges + op.idx;
-            if constexpr (CL) {
-              xpar ^= 1u;
-              unsigned char* b0 = cbuf + (size_t)(2 * xpar) * cbuf_one;
-              exchange_global<false>(ps, ps, b0, b0, S.xbase[X->base + tig], S.xbase[X->base + G + tig], X->woff, X->roff, gsync);
-            } else exchange(ps, S.xbuf | S.xbase[X->base + tig], S.xbuf | S.xbase[X->base + G + tig], X->woff, X->roff, gsync);
-          } break;
-          default: break;
-        }
-        op = next;
-        cfa = ncfa;
-      }
-    }
-    }  // forward program (skipped when the backward pass starts from a saved state)
-
-    if constexpr (!BWD && STATE) {
-#pragma unroll
-      for (int q = 0; q < NA / 2; ++q)
-        __stcs(st_rows + (size_t)q * G, make_float4(ps[2 * q].x, ps[2 * q].y, ps[2 * q + 1].x, ps[2 * q + 1].y));
-    }
-
-    if constexpr (!BWD) {
-      // ================= measurement: <Z> per physical bit =================
-      float2 tot2, S2[kR];
-      signed_sums2([&](int j) { return __fmul2_rn(ps[j], ps[j]); }, tot2, S2);
-      const float tot = tot2.x + tot2.y;
-      // per-warp partials: [0..4] register bits, [5..9] lane bits, [10] plain total (for the warp bits)
-      float val[11];
-#pragma unroll
-      for (int r = 0; r < kR; ++r) val[r] = sample_sum(S2[r].x + S2[r].y, lbits);
-#pragma unroll
-      for (int b = 0; b < 5; ++b) val[kR + b] = (b < lbits) ? sample_sum(((lane >> b) & 1) ? -tot : tot, lbits) : 0.f;
-      val[10] = sample_sum(tot, lbits);
-      if (wbits == 0) {
-        if (active && tis == 0) {
-          float* yrow = a.y + (size_t)bs * a.n;
-#pragma unroll
-          for (int pb = 0; pb < 10; ++pb)
-            if (pb < a.n) yrow[a.wire_of_bit[pb]] = val[pb];
-        }
-      } else {
-        // a sample spans 2^wb warps: combine their partials through shared (or, for a cluster, global)
-        // memory in a fixed order
-        float* const mine = CL ? cred + (size_t)gw * 48 : red;
-        if (lane == 0) {
-#pragma unroll
-          for (int c = 0; c < 11; ++c) { if (CL) __stcg(mine + c, val[c]); else mine[c] = val[c]; }
-        }
-        gsync();
-        if (gw == 0 && lane < a.n && active) {
-          const float* r0 = CL ? cred : S.red + (size_t)(grp << wbits) * 16;
-          const int stride = CL ? 48 : 16;
-          float t = 0.f;
-          for (int w = 0; w < gwarps; ++w) {
-            const float v = CL ? __ldcg(r0 + w * stride + (lane < 10 ? lane : 10)) : r0[w * stride + (lane < 10 ? lane : 10)];
-            t += (lane >= 10 && ((w >> (lane - 10)) & 1)) ? -v : v;
-          }
-          a.y[(size_t)bs * a.n + a.wire_of_bit[lane]] = t;
-        }
-      }
-    } else {
-      // ================= seed lam = (sum_q gy_q Z_q) psi =================
-      float2 ls[NA];
-      {
-        float g[kR + kMaxThreadBits];
-        const float* gyrow = a.gy + (size_t)(active ? bs : 0) * a.n;
-#pragma unroll
-        for (int pb = 0; pb < kR + kMaxThreadBits; ++pb) g[pb] = (active && pb < a.n) ? gyrow[a.wire_of_bit[pb]] : 0.f;
-        float cl = 0.f;
-#pragma unroll
-        for (int b = 0; b < kMaxThreadBits; ++b) cl += ((tis >> b) & 1) ? -g[kR + b] : g[kR + b];
-        float cj[NA];
-        cj[0] = cl + g[0] + g[1] + g[2] + g[3] + g[4];
-#pragma unroll
-        for (int j = 1; j < NA; ++j) {
-          const int low = j & (-j);                      // lowest set bit
-          const int r = low == 1 ? 0 : low == 2 ? 1 : low == 4 ? 2 : low == 8 ? 3 : 4;
-          cj[j] = fmaf(-2.f, g[r], cj[j ^ low]);
-        }
-#pragma unroll
-        for (int j = 0; j < NA; ++j) ls[j] = mul2(cj[j], ps[j]);
-      }
-      // ================= reverse program =================
-      MicroOp op = S.ops[a.n_ops - 2];
-      float4 cfa = *reinterpret_cast<const float4*>(S.coef + op.pad1 * 8);
-      for (int pc = a.n_ops - 2; pc >= 0; --pc) {
-        const MicroOp next = S.ops[pc > 0 ? pc - 1 : 0];
-        const float4 ncfa = *reinterpret_cast<const float4*>(S.coef + next.pad1 * 8);
-        switch (op.pad0) {
-#define H_CASE_ROT(RB) case H_ROT + RB: { float v = rot_grad<RB>(ps, ls); rot<RB>(ps, -cfa.x, -cfa.y); rot<RB>(ls, -cfa.x, -cfa.y); \
-            if (op.acc >= 0) { v = warp_sum(v); if (lane == 0) wacc[op.acc] += v; } } break;
-          H_CASE_ROT(0) H_CASE_ROT(1) H_CASE_ROT(2) H_CASE_ROT(3) H_CASE_ROT(4)
-#undef H_CASE_ROT
-#define H_CASE_ROTX(RB) case H_ROTX + RB: { const float2 ab = xc[op.idx]; float v = rot_grad<RB>(ps, ls); rot<RB>(ps, -ab.x, -ab.y); rot<RB>(ls, -ab.x, -ab.y); \
-            v = sample_sum(v, lbits); if ((lane & ((1 << lbits) - 1)) == 0) gxacc[siw * n_ang + op.idx] += v; } break;
-          H_CASE_ROTX(0) H_CASE_ROTX(1) H_CASE_ROTX(2) H_CASE_ROTX(3) H_CASE_ROTX(4)
-#undef H_CASE_ROTX
-#define CU3_REDUCE(A, ACC)                                                                                  \
-            if ((ACC) >= 0) {                                                                               \
-              const float r = warp_sum4((A.v0.x + A.v0.y) - (A.v1.x + A.v1.y), -2.f * (A.qp.x - A.qp.y),    \
-                                        -2.f * (A.ql.x - A.ql.y), 0.f, lane);                               \
-              if ((lane & 7) == 0 && (lane >> 3) < 3) wacc[(ACC) + (lane >> 3)] += r;                       \
-            }
-#define H_CASE_CU3L(RT, RC) case H_CU3L + RT * 4 + (RC < RT ? RC : RC - 1): { const float2 z = make_float2(0.f, 0.f); Cu3Acc A{z, z, z, z}; \
-            const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), true); cu3_loc_bwd<RT, RC>(ps, ls, g, A); CU3_REDUCE(A, op.acc) } break;
-          H_CASE_CU3L(0, 1) H_CASE_CU3L(0, 2) H_CASE_CU3L(0, 3) H_CASE_CU3L(0, 4)
-          H_CASE_CU3L(1, 0) H_CASE_CU3L(1, 2) H_CASE_CU3L(1, 3) H_CASE_CU3L(1, 4)
-          H_CASE_CU3L(2, 0) H_CASE_CU3L(2, 1) H_CASE_CU3L(2, 3) H_CASE_CU3L(2, 4)
-          H_CASE_CU3L(3, 0) H_CASE_CU3L(3, 1) H_CASE_CU3L(3, 2) H_CASE_CU3L(3, 4)
-          H_CASE_CU3L(4, 0) H_CASE_CU3L(4, 1) H_CASE_CU3L(4, 2) H_CASE_CU3L(4, 3)
-#undef H_CASE_CU3L
-#define H_CASE_CU3P(RB) case H_CU3P + RB: { const float2 z = make_float2(0.f, 0.f); Cu3Acc A{z, z, z, z}; \
-            if (__popc(tis & op.aux) & 1) { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), true); cu3_all_bwd<RB>(ps, ls, g, A); } \
-            CU3_REDUCE(A, op.acc) } break;
-          H_CASE_CU3P(0) H_CASE_CU3P(1) H_CASE_CU3P(2) H_CASE_CU3P(3) H_CASE_CU3P(4)
-#undef H_CASE_CU3P
-          case H_ROT5: {
-            float v[5];
-#define ROT5_STEP(K)                                                                                       \
-            {                                                                                              \
-              const int pos = (op.aux >> (3 * K)) & 7;                                                     \
-              const float2 ab = *reinterpret_cast<const float2*>(S.coef + (op.idx + pos) * 8);             \
-              v[K] = rot_grad<K>(ps, ls);                                                                  \
-              rot<K>(ps, -ab.x, -ab.y); rot<K>(ls, -ab.x, -ab.y);                                          \
-            }
-            ROT5_STEP(4) ROT5_STEP(3) ROT5_STEP(2) ROT5_STEP(1) ROT5_STEP(0)
-#undef ROT5_STEP
-            // five sums in one halving butterfly: lane 8k' ... holds component (lane >> 2)
-            const float t8[16] = {v[0], v[1], v[2], v[3], v[4], 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-            const float r = warp_sum16(t8, lane);
-            if ((lane & 1) == 0 && (lane >> 1) < 5) wacc[op.acc + ((op.aux >> (3 * (lane >> 1))) & 7)] += r;
-          } break;
-          case H_ROTX5: {
-#define ROTX5_STEP(K)                                                                                      \
-            {                                                                                              \
-              const int col = (op.idx >> (5 * K)) & 31;                                                    \
-              const float2 ab = xc[col];                                                                   \
-              float v = rot_grad<K>(ps, ls);                                                               \
-              rot<K>(ps, -ab.x, -ab.y); rot<K>(ls, -ab.x, -ab.y);                                          \
-              v = sample_sum(v, lbits);                                                                    \
-              if ((lane & ((1 << lbits) - 1)) == 0) gxacc[siw * n_ang + col] += v;                          \
-            }
-            ROTX5_STEP(4) ROTX5_STEP(3) ROTX5_STEP(2) ROTX5_STEP(1) ROTX5_STEP(0)
-#undef ROTX5_STEP
-          } break;
-          case H_CHAIN: {
-#define CHAIN_STEP(K, RT, RC)                                                                              \
-            {                                                                                              \
-              const float2 z = make_float2(0.f, 0.f);                                                      \
-              Cu3Acc A{z, z, z, z};                                                                        \
-              const Cu3 g = load_cu3(S.coef + (op.idx + K) * 8, true);                                     \
-              cu3_loc_bwd<RT, RC>(ps, ls, g, A);                                                           \
-              CU3_REDUCE(A, op.acc + 3 * K)                                                                \
-            }
-            CHAIN_STEP(3, 4, 3)
-            CHAIN_STEP(2, 3, 2)
-            CHAIN_STEP(1, 2, 1)
-            CHAIN_STEP(0, 1, 0)
-#undef CHAIN_STEP
-          } break;
-#undef CU3_REDUCE
-          case H_DIAG:
-          case H_DIAGR: {
-            const DiagDesc* D = S.diags + op.aux;
-            float2 tot2, S2[kR];
-            // Im(conj(lam) psi) = lam.re psi.im - lam.im psi.re, kept as the pair (lam.re psi.im, lam.im psi.re)
-            signed_sums2([&](int j) { return __fmul2_rn(ls[j], swp(ps[j])); }, tot2, S2);
-            const float tot = tot2.x - tot2.y;
-            // all (up to ten) per-bit sums in one halving butterfly; lane l ends up with component l >> 1
-            float t16[16];
-#pragma unroll
-            for (int r = 0; r < kR; ++r) t16[r] = S2[r].x - S2[r].y;
-#pragma unroll
-            for (int b = 0; b < kMaxThreadBits; ++b) t16[kR + b] = ((tis >> b) & 1) ? -tot : tot;
-#pragma unroll
-            for (int k = kR + kMaxThreadBits; k < 16; ++k) t16[k] = 0.f;
-            const float r = warp_sum16(t16, lane);
-            if ((lane & 1) == 0) {
-              const int comp = lane >> 1;
-              const int ai = comp < kR ? D->acc_reg[comp]
-                                       : (comp < kR + kMaxThreadBits && op.pad0 == H_DIAG ? D->acc_thr[comp - kR] : -1);
-              if (ai >= 0) wacc[ai] += r;
-            }
-            if (op.pad0 == H_DIAG) diag_mul<true, true>(ps, ls, S.big + (size_t)op.idx * 32 * G, G, tig);
-            else diag_mul<true, true>(ps, ls, S.small + op.idx * 32, 1, 0);
-          } break;
-          case H_XCHG: {   // inverse: roles of the two address sets swapped
-            const Exchange* X = S.exchanges + op.idx;
-            if constexpr (CL) {
-              const uint32_t wa = S.xbase[X->base + G + tig], ra = S.xbase[X->base + tig];
-              xpar ^= 1u;
-              unsigned char* b0 = cbuf + (size_t)(2 * xpar) * cbuf_one;
-              exchange_global<true>(ps, ls, b0, b0 + cbuf_one, wa, ra, X->roff, X->woff, gsync);
-            } else {
-              const uint32_t wa = S.xbuf | S.xbase[X->base + G + tig], ra = S.xbuf | S.xbase[X->base + tig];
-              exchange(ps, wa, ra, X->roff, X->woff, gsync);
-              exchange(ls, wa, ra, X->roff, X->woff, gsync);
-            }
-          } break;
-          default: break;
-        }
-        op = next;
-        cfa = ncfa;
-      }
-      // ================= input gradients of this group's samples =================
-      if (GEOM == 0 && a.amplitude) {
-        // psi0 = x / |x|:  dL/dx = (g - psi0 (psi0 . g)) / |x|  with g = 2 Re(lam0), in the initial layout
-        if (a.gx != nullptr) {
-          const float* xr = a.x + (size_t)(active ? bs : 0) * a.n_inputs;
-          float* gxr = a.gx + (size_t)(active ? bs : 0) * a.n_inputs;
-          float xv[NA], ss = 0.f, dot = 0.f;
-#pragma unroll
-          for (int j = 0; j < NA; ++j) {
-            const unsigned k = klog_t | klog((unsigned)j);
-            xv[j] = (active && (int)k < a.n_inputs) ? xr[k] : 0.f;
-            ss = fmaf(xv[j], xv[j], ss);
-            dot = fmaf(xv[j], 2.f * ls[j].x, dot);
-          }
-          const float inv = rsqrtf(sample_sum(ss, lbits));
-          dot = sample_sum(dot, lbits) * inv;
-#pragma unroll
-          for (int j = 0; j < NA; ++j) {
-            const unsigned k = klog_t | klog((unsigned)j);
-            if (active && (int)k < a.n_inputs) gxr[k] = (2.f * ls[j].x - xv[j] * inv * dot) * inv;
-          }
-          if (active && a.n_inputs > (1 << a.n))          // columns beyond 2^n never enter the state
-            for (int k = (1 << a.n) + tis; k < a.n_inputs; k += (1 << tb)) gxr[k] = 0.f;
-        }
-        continue;
-      }
-      if constexpr (CL) {   // publish this warp's partial sums to the cluster scratch
-        for (int i = lane; i < n_ang; i += 32) __stcg(cred + (size_t)gw * 48 + 16 + i, gxacc[i]);
-      }
-      gsync();
-      if (a.gx != nullptr && gw == 0) {
-        for (int i = lane; i < spw * n_ang; i += 32) {
-          const long long bb = wb * spw + i / n_ang;
-          float t = 0.f;
-          for (int w = 0; w < gwarps; ++w)                                   // the group's warps, fixed order
-            t += CL ? __ldcg(cred + (size_t)w * 48 + 16 + i) : gxacc[(size_t)w * spw * max(n_ang, 1) + i];
-          if (bb < a.B) a.gx[(size_t)bb * a.n_inputs + (i % n_ang)] = t;
-        }
-      }
-      gsync();
-      for (int i = lane; i < spw * n_ang; i += 32) gxacc[i] = 0.f;
-    }
-  }
-
-  if constexpr (BWD) {
-    __syncthreads();
-    for (int i = threadIdx.x; i < a.n_acc; i += blockDim.x) {
-      float s = 0.f;
-#pragma unroll 1
-      for (int w = 0; w < WARPS; ++w) s += S.wacc[(size_t)w * a.n_acc + i];
-      a.partial[(size_t)blockIdx.x * a.n_acc + i] = s;
-    }
-  }
 }
 
 // ---- per-call tables: gate coefficients (double-precision trig) and merged diagonals -----------------
@@ -891,7 +85,7 @@ __global__ void k_vm_prep(const DevOp* __restrict__ coef_ops, int n_coef, const 
         const double phi = (tm.src == QNN_SRC_CONST) ? (double)tm.value : (double)w[tm.src];
         ang += ((p >> tm.bit0) & 1u) ? 0.5 * phi : -0.5 * phi;
       } else if (((p >> tm.bit0) & 1u) && ((p >> tm.bit1) & 1u)) {
-        ang += 3.14159265358979323846;
+        ang += tm.kind == 1 ? 3.14159265358979323846 : ((tm.src == QNN_SRC_CONST) ? (double)tm.value : (double)w[tm.src]);
       }
     }
     double s, c;
@@ -926,11 +120,6 @@ size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
 constexpr size_t kSmemMax = 227 * 1024;
 constexpr int kFwdThreads = 512, kBwdThreads = 256;   // 16 / 8 warps per CTA, one CTA per SM (124 / 231 registers)
 
-template <typename K>
-int set_smem(K kern, size_t bytes) {
-  if (bytes > 48 * 1024) QNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-  return QNN_OK;
-}
 
 void fill_args(const qnn_circuit* c, const Program& p, const Plan& pl, void* ws, bool bwd, VmArgs* a) {
   unsigned char* wsb = static_cast<unsigned char*>(ws);
@@ -948,7 +137,11 @@ void fill_args(const qnn_circuit* c, const Program& p, const Plan& pl, void* ws,
   a->n_angle = p.amplitude ? 0 : c->n_inputs;
   for (int w = 0; w < 16; ++w) a->init_bit_of_wire[w] = w < p.n ? (int8_t)p.initial_bit_of_wire[w] : 0;
   const int threads = bwd ? kBwdThreads : pl.fwd_threads;
-  a->table_bytes = (unsigned)table_bytes(p, p.amplitude ? 0 : c->n_inputs, threads / 32, bwd, pl.cluster > 0);
+  const TableLayout tl = table_layout(p, p.amplitude ? 0 : c->n_inputs, threads / 32, bwd, pl.cluster > 0);
+  a->table_bytes = tl.total;
+  a->off.ops = tl.ops; a->off.exch = tl.exch; a->off.xbase = tl.xbase; a->off.diags = tl.diags; a->off.coef = tl.coef;
+  a->off.big = tl.big; a->off.small = tl.small; a->off.xcoef = tl.xcoef; a->off.red = tl.red; a->off.wacc = tl.wacc;
+  a->off.gxacc = tl.gxacc;
   for (int b = 0; b < 16; ++b) a->wire_of_bit[b] = 0;
   for (int w = 0; w < p.n; ++w) a->wire_of_bit[p.final_bit_of_wire[w]] = (int8_t)w;
   a->partial = reinterpret_cast<float*>(wsb + pl.ws_coef + pl.ws_diag);
@@ -981,10 +174,6 @@ size_t state_bytes(const Program& p, int64_t B) {
   return (size_t)n_batches(p, B) * ((size_t)kWarpAmps << p.wb) * sizeof(float2);
 }
 
-// How many clusters of `cluster` CTAs can be resident at once (GPC boundaries strand some SMs, so this is
-// less than 148 / cluster); a persistent cluster beyond that number would run as a second wave.
-static int max_active_clusters(int cluster, size_t smem);
-
 bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
   if (!p.ok) return false;
   const int bwd_warps = kBwdThreads / 32;
@@ -999,7 +188,7 @@ bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
     out->smem_fwd = smem_bytes(p, n_ang_in, bwd_warps, false, true);
     out->smem_bwd = smem_bytes(p, n_ang_in, bwd_warps, true, true);
     if (out->smem_fwd > kSmemMax || out->smem_bwd > kSmemMax) return false;
-    out->n_clusters = (int)std::max<int64_t>(1, std::min<int64_t>(B, max_active_clusters(out->cluster, out->smem_bwd)));
+    out->n_clusters = (int)std::max<int64_t>(1, std::min<int64_t>(B, max_active_clusters_g2(out->cluster, out->smem_bwd)));
     out->grid = out->n_clusters * out->cluster;
     out->ws_cluster = align256(((size_t)out->n_clusters << (p.n + 5)) + (size_t)out->n_clusters * (1 << p.wb) * 48 * sizeof(float));
   } else {
@@ -1064,49 +253,6 @@ void release(Program* p) {
   p->d_exchanges = nullptr; p->d_xbase = nullptr; p->d_slots = nullptr; p->d_slot_ptr = nullptr; p->d_slot_idx = nullptr;
 }
 
-// Plain launch, or a cluster launch (cudaLaunchKernelEx) when a sample spans several CTAs.
-template <typename K>
-int launch_vm(K kern, const Plan& pl, int grid, int threads, size_t smem, const VmArgs& a, cudaStream_t st) {
-  int r = set_smem(kern, smem);
-  if (r) return r;
-  if (pl.cluster == 0) {
-    kern<<<grid, threads, smem, st>>>(a);
-  } else {
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(threads); cfg.dynamicSmemBytes = smem; cfg.stream = st;
-    cudaLaunchAttribute attr{};
-    attr.id = cudaLaunchAttributeClusterDimension;
-    attr.val.clusterDim.x = pl.cluster; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
-    cfg.attrs = &attr; cfg.numAttrs = 1;
-    QNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, a));
-  }
-  QNN_CUDA_CHECK(cudaGetLastError());
-  return QNN_OK;
-}
-
-static int max_active_clusters(int cluster, size_t smem) {
-  static int cache[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
-  if (cluster < 1 || cluster > 8) return 1;
-  if (cache[cluster] > 0) return cache[cluster];
-  int n = 148 / cluster;
-  auto kern = k_vm<true, kBwdThreads, 1, false, 2>;
-  if (smem <= kSmemMax && cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemMax) == cudaSuccess) {
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(148 / cluster * cluster); cfg.blockDim = dim3(kBwdThreads); cfg.dynamicSmemBytes = smem;
-    cudaLaunchAttribute attr{};
-    attr.id = cudaLaunchAttributeClusterDimension;
-    attr.val.clusterDim.x = cluster; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
-    cfg.attrs = &attr; cfg.numAttrs = 1;
-    int q = 0;
-    if (cudaOccupancyMaxActiveClusters(&q, kern, &cfg) == cudaSuccess && q > 0) n = std::min(n, q);
-    else (void)cudaGetLastError();
-  } else {
-    (void)cudaGetLastError();
-  }
-  cache[cluster] = n;
-  return n;
-}
-
 int forward(const qnn_circuit* c, const Program& p, const Plan& pl, const float* x, const float* w, float* y,
             int64_t B, void* ws, float* state, cudaStream_t st) {
   VmArgs a{};
@@ -1120,10 +266,11 @@ int forward(const qnn_circuit* c, const Program& p, const Plan& pl, const float*
     const int64_t ctas = (n_batches(p, B) + groups_per_cta - 1) / groups_per_cta;
     grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, 148));
   }
-  auto go = [&](auto kern) { return launch_vm(kern, pl, grid, pl.fwd_threads, pl.smem_fwd, a, st); };
-  if (pl.cluster > 0) return a.state ? go(k_vm<false, kFwdThreads, 1, true, 2>) : go(k_vm<false, kFwdThreads, 1, false, 2>);
-  if (p.wb > 0) return a.state ? go(k_vm<false, kFwdThreads, 1, true, 1>) : go(k_vm<false, kFwdThreads, 1, false, 1>);
-  return a.state ? go(k_vm<false, kFwdThreads, 1, true, 0>) : go(k_vm<false, kFwdThreads, 1, false, 0>);
+  const LaunchCfg lc{grid, pl.fwd_threads, pl.cluster, pl.smem_fwd, st};
+  const bool state_on = a.state != nullptr;
+  if (pl.cluster > 0) return launch_g2(false, state_on, lc, a);
+  if (p.wb > 0) return launch_g1(false, state_on, lc, a);
+  return p.amplitude ? launch_g0a(false, state_on, lc, a) : launch_g0(false, state_on, lc, a);
 }
 
 int backward(const qnn_circuit* c, const Program& p, const Plan& pl, const float* x, const float* w,
@@ -1133,10 +280,11 @@ int backward(const qnn_circuit* c, const Program& p, const Plan& pl, const float
   a.x = x; a.gy = gy; a.gx = gx; a.B = B; a.state = reinterpret_cast<float4*>(const_cast<float*>(state));
   int rc = launch_prep(p, w, a, st);
   if (rc) return rc;
-  auto go = [&](auto kern) { return launch_vm(kern, pl, pl.grid, kBwdThreads, pl.smem_bwd, a, st); };
-  if (pl.cluster > 0) rc = a.state ? go(k_vm<true, kBwdThreads, 1, true, 2>) : go(k_vm<true, kBwdThreads, 1, false, 2>);
-  else if (p.wb > 0) rc = a.state ? go(k_vm<true, kBwdThreads, 1, true, 1>) : go(k_vm<true, kBwdThreads, 1, false, 1>);
-  else rc = a.state ? go(k_vm<true, kBwdThreads, 1, true, 0>) : go(k_vm<true, kBwdThreads, 1, false, 0>);
+  const LaunchCfg lc{pl.grid, kBwdThreads, pl.cluster, pl.smem_bwd, st};
+  const bool state_on = a.state != nullptr;
+  if (pl.cluster > 0) rc = launch_g2(true, state_on, lc, a);
+  else if (p.wb > 0) rc = launch_g1(true, state_on, lc, a);
+  else rc = p.amplitude ? launch_g0a(true, state_on, lc, a) : launch_g0(true, state_on, lc, a);
   if (rc) return rc;
   if (c->n_weights > 0) {
     k_vm_finalize<<<c->n_weights, 128, 0, st>>>(a.partial, pl.grid, p.n_acc, p.d_slots, p.d_slot_ptr, p.d_slot_idx, gw);

@@ -32,7 +32,8 @@ enum MopKind : int32_t {
   MOP_ROT = 1,        // real rotation RY on register bit a, applied in place as three shears; coef row idx; acc (1)
   MOP_ROT_X = 2,      // same, angle = x[b, idx] (per sample); gradient goes to gx
   MOP_CU3_L = 4,      // controlled U3 = diag(1,e^{i phi}) RY(theta) diag(1,e^{i lambda}) on the control=1 pairs:
-                      //   target register bit a, control register bit b; coef row idx; acc (3: theta, phi, lambda)
+                      //   target register bit a, control register bit b & 7; coef row idx; acc (3: theta, phi, lambda);
+                      //   b & kCu3InlinePost: the e^{i phi} phase is applied here (else it was deferred into a DIAG)
   MOP_CU3_P = 5,      // same with control = parity(lane_in_sample & aux)
   MOP_DIAG = 6,       // multiply by diagonal table idx ([j][lane], 1024 entries); desc aux
   MOP_DIAG_REG = 7,   // diagonal that depends on register bits only (32-entry table idx); desc aux
@@ -41,8 +42,11 @@ enum MopKind : int32_t {
   MOP_ROT5 = 9,       // rotations on all five register bits; bit k uses coef row idx + pos_k and accumulator
                       //   acc + pos_k, pos_k = (aux >> 3k) & 7
   MOP_ROTX5 = 10,     // per-sample rotations on all five register bits; bit k uses x column (idx >> 5k) & 31
-  MOP_CU3_CHAIN = 11, // CU3_L (t,c) = (1,0), (2,1), (3,2), (4,3) in that order; rows idx..idx+3, accs acc + 3k
+  MOP_CU3_CHAIN = 11, // CU3_L (t,c) = (1,0), (2,1), (3,2), (4,3) in that order; rows idx..idx+3, accs acc + 3k;
+                      //   aux bit k: gate k applies its post-phase inline
 };
+
+constexpr int32_t kCu3InlinePost = 8;
 
 struct MicroOp {       // 32 bytes
   int32_t kind, a, b, idx, acc, aux;
@@ -56,7 +60,7 @@ enum Handler : int32_t {
 };
 
 struct DiagTerm {      // one factor of a diagonal: RZ(angle) on a physical bit, or CZ on two bits
-  int32_t kind;        // 0: RZ, 1: CZ
+  int32_t kind;        // 0: RZ, 1: CZ, 2: controlled phase e^{i angle} where both bits are 1 (a deferred CU3 post-phase)
   int32_t src;         // RZ angle source (qnn_op convention), QNN_SRC_CONST -> value
   float value;
   int32_t bit0, bit1;  // physical bit(s), in the layout current when the diagonal is applied

@@ -10,6 +10,7 @@
 //      collected and applied as one table multiply.
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <sstream>
 
@@ -18,7 +19,7 @@
 namespace vm {
 namespace {
 
-enum ItemKind { IT_REAL, IT_RZ, IT_CZ, IT_CNOT, IT_CGEN };
+enum ItemKind { IT_REAL, IT_RZ, IT_CZ, IT_CP, IT_CNOT, IT_CGEN };
 
 struct Item {
   ItemKind kind;
@@ -27,6 +28,7 @@ struct Item {
   int32_t src[3];
   float value[3];
   bool done = false;
+  bool inline_post = true;   // IT_CGEN: the e^{i phi} phase is applied inside the gate body (else deferred as IT_CP)
 };
 
 inline int ctz(uint32_t v) { return __builtin_ctz(v); }
@@ -137,12 +139,20 @@ struct Builder {
           }
           it.kind = IT_CGEN; it.w0 = o.wire0; it.w1 = o.wire1; it.gate = QNN_CU3;
           items.push_back(it);
+          {   // placeholder for the deferred post-phase e^{i phi} on (control = 1, target = 1); see defer_phases()
+            Item cp{};
+            for (int k = 0; k < 3; ++k) { cp.src[k] = QNN_SRC_CONST; cp.value[k] = 0.f; }
+            cp.kind = IT_CP; cp.w0 = o.wire0; cp.w1 = o.wire1; cp.gate = QNN_CZ;
+            cp.src[0] = o.src[1]; cp.value[0] = o.value[1];
+            items.push_back(cp);
+          }
           break;
         default:
           P->why_not = "unknown gate";
           return false;
       }
     }
+    defer_phases();
     by_wire.assign(n, {});
     for (size_t i = 0; i < items.size(); ++i) {
       by_wire[items[i].w0].push_back((int)i);
@@ -150,6 +160,32 @@ struct Builder {
     }
     head.assign(n, 0);
     return true;
+  }
+
+  // CU3 = diag(1, e^{i phi}) R diag(1, e^{i lambda}) on the control = 1 block.  The post-phase is a
+  // diagonal on (control, target): it commutes with every later gate that does not TARGET one of the two
+  // wires, so it can ride along with a later merged diagonal for free.  Defer it when the next gate that
+  // targets either wire is a single-qubit rotation (which flushes a diagonal anyway) or when there is none
+  // (a trailing diagonal: no effect on <Z>); keep it inside the gate body when a controlled gate or a CNOT
+  // would otherwise force a diagonal of its own.
+  void defer_phases() {
+    static const bool no_defer = [] { const char* e = getenv("QNN_VM_NO_DEFER"); return e && e[0] == '1'; }();   // A/B knob
+    std::vector<Item> out;
+    for (size_t i = 0; i < items.size(); ++i) {
+      if (items[i].kind == IT_CP) continue;                   // placeholders are re-emitted below
+      out.push_back(items[i]);
+      if (items[i].kind != IT_CGEN) continue;
+      const int c = items[i].w0, t = items[i].w1;
+      bool defer = !no_defer;
+      for (size_t k = i + 2; defer && k < items.size(); ++k) {
+        const Item& nx = items[k];
+        const int target = (nx.kind == IT_REAL) ? nx.w0 : (nx.kind == IT_CGEN || nx.kind == IT_CNOT) ? nx.w1 : -1;
+        if (target == c || target == t) { defer = nx.kind == IT_REAL; break; }
+      }
+      out.back().inline_post = !defer;
+      if (defer) out.push_back(items[i + 1]);                 // the IT_CP placeholder right behind the gate
+    }
+    items.swap(out);
   }
 
   bool ready(int i) const {
@@ -198,10 +234,10 @@ struct Builder {
     for (int i : pending) {
       const Item& it = items[i];
       DiagTerm t{};
-      t.kind = it.kind == IT_CZ ? 1 : 0;
+      t.kind = it.kind == IT_CZ ? 1 : it.kind == IT_CP ? 2 : 0;
       t.src = it.src[0]; t.value = it.value[0];
       t.bit0 = bit_of(it.w0);
-      t.bit1 = it.kind == IT_CZ ? bit_of(it.w1) : -1;
+      t.bit1 = it.kind == IT_RZ ? -1 : bit_of(it.w1);
       if (t.bit0 >= kR || t.bit1 >= kR) reg_only = false;
       if (t.kind == 0 && t.src >= 0) {
         int32_t& a = t.bit0 < kR ? D.acc_reg[t.bit0] : D.acc_thr[t.bit0 - kR];
@@ -227,7 +263,8 @@ struct Builder {
     const Item& it = items[i];
     switch (it.kind) {
       case IT_RZ: return row_unit(it.w0) ? ST_OK : ST_BLOCKED;
-      case IT_CZ: return (row_unit(it.w0) && row_unit(it.w1)) ? ST_OK : ST_BLOCKED;
+      case IT_CZ:
+      case IT_CP: return (row_unit(it.w0) && row_unit(it.w1)) ? ST_OK : ST_BLOCKED;
       case IT_CNOT: return pending_on(it.w1) ? ST_NEEDS_FLUSH : ST_OK;
       case IT_REAL:
         if (!clean(it.w0) || bit_of(it.w0) >= kR) return ST_BLOCKED;
@@ -248,6 +285,7 @@ struct Builder {
         pending.push_back(i);
         return true;
       case IT_CZ:
+      case IT_CP:
         if (!row_unit(it.w0) || !row_unit(it.w1)) return false;
         pending.push_back(i);
         return true;
@@ -277,6 +315,7 @@ struct Builder {
         const int cb = bit_of(it.w0);
         if (cb < kR) { m.kind = MOP_CU3_L; m.b = cb; }
         else { m.kind = MOP_CU3_P; m.aux = 1 << (cb - kR); }   // thread-bit mask (lanes, then warps)
+        if (it.inline_post) m.b |= kCu3InlinePost;
         m.idx = new_coef_row(QNN_CU3, it.src, it.value, 3);
         bool any_w = false;
         for (int k = 0; k < 3; ++k) any_w |= it.src[k] >= 0;
@@ -419,12 +458,13 @@ struct Builder {
       bool chain = i + 4 <= in.size();
       for (int k = 0; chain && k < 4; ++k) {
         const MicroOp& m = in[i + k];
-        chain = m.kind == MOP_CU3_L && m.a == k + 1 && m.b == k && m.idx == in[i].idx + k && in[i].acc >= 0 &&
+        chain = m.kind == MOP_CU3_L && m.a == k + 1 && (m.b & 7) == k && m.idx == in[i].idx + k && in[i].acc >= 0 &&
                 m.acc == in[i].acc + 3 * k;
       }
       if (chain) {
         MicroOp m{};
         m.kind = MOP_CU3_CHAIN; m.idx = in[i].idx; m.acc = in[i].acc;
+        for (int k = 0; k < 4; ++k) if (in[i + k].b & kCu3InlinePost) m.aux |= 1 << k;   // per-gate inline post-phase
         out.push_back(m);
         i += 4;
         continue;
@@ -442,7 +482,7 @@ struct Builder {
       switch (m.kind) {
         case MOP_ROT: m.pad0 = H_ROT + m.a; m.pad1 = m.idx; break;
         case MOP_ROT_X: m.pad0 = H_ROTX + m.a; break;
-        case MOP_CU3_L: m.pad0 = H_CU3L + m.a * 4 + (m.b < m.a ? m.b : m.b - 1); m.pad1 = m.idx; break;
+        case MOP_CU3_L: m.pad0 = H_CU3L + m.a * 4 + ((m.b & 7) < m.a ? (m.b & 7) : (m.b & 7) - 1); m.pad1 = m.idx; break;
         case MOP_CU3_P: m.pad0 = H_CU3P + m.a; m.pad1 = m.idx; break;
         case MOP_DIAG: m.pad0 = H_DIAG; break;
         case MOP_DIAG_REG: m.pad0 = H_DIAGR; break;

@@ -99,9 +99,12 @@ def emulate_forward(desc, x, w):
             stats["g1"] += 1
         elif kind in (MOP_CG1_L, MOP_CG1_P):
             co = desc["coef_ops"][idx]
-            U = _matrix(U3, [_angle(s_, v_, w) for s_, v_ in zip(co["src"], co["value"])])
+            ang = [_angle(s_, v_, w) for s_, v_ in zip(co["src"], co["value"])]
+            if not (b & 8):                      # post-phase e^{i phi} deferred into a later diagonal
+                ang[1] = 0.0
+            U = _matrix(U3, ang)
             if kind == MOP_CG1_L:
-                _apply_reg(state, U, a, ctrl_rbit=b)
+                _apply_reg(state, U, a, ctrl_rbit=b & 7)
                 stats["cg_l"] += 1
             else:
                 par = np.array([bin(int(v) & aux).count("1") & 1 for v in lis], bool)
@@ -121,8 +124,10 @@ def emulate_forward(desc, x, w):
         elif kind == MOP_CU3_CHAIN:
             for k in range(4):
                 co = desc["coef_ops"][idx + k]
-                U = _matrix(U3, [_angle(s_, v_, w) for s_, v_ in zip(co["src"], co["value"])])
-                _apply_reg(state, U, k + 1, ctrl_rbit=k)
+                ang = [_angle(s_, v_, w) for s_, v_ in zip(co["src"], co["value"])]
+                if not ((aux >> k) & 1):
+                    ang[1] = 0.0
+                _apply_reg(state, _matrix(U3, ang), k + 1, ctrl_rbit=k)
             stats["cg_l"] += 4
         elif kind in (MOP_DIAG, MOP_DIAG_REG):
             D = desc["diags"][aux]
@@ -134,8 +139,10 @@ def emulate_forward(desc, x, w):
                 if tkind == 0:
                     z = 1 - 2 * ((p >> bit0) & 1)
                     ang += -0.5 * _angle(src, value, w) * z
-                else:
+                elif tkind == 1:
                     ang += np.pi * (((p >> bit0) & 1) & ((p >> bit1) & 1))
+                else:                              # deferred CU3 post-phase: e^{i phi} where both bits are 1
+                    ang += _angle(src, value, w) * (((p >> bit0) & 1) & ((p >> bit1) & 1))
                 if kind == MOP_DIAG_REG:
                     assert bit0 < 5 and bit1 < 5
             state *= np.exp(1j * ang)
