@@ -389,8 +389,18 @@ __device__ __forceinline__ float2 rot_coef_x(float xv) {
   return make_float2(-sh / ch, 2.f * sh * ch);
 }
 
+// Shared-memory form of a micro-op, built once per CTA: what the handlers read, plus the first half of the
+// op's coefficient row, so that one dispatch is two consecutive 16-byte loads (no dependent second load).
+struct __align__(16) SOp {
+  int h;        // handler id | kPostBit when a CU3 applies its post-phase inline
+  int idx, acc, aux;
+  float4 cf;    // coefficient row [0..3] of the op (zero row if it has none)
+};
+static_assert(sizeof(SOp) == sizeof(MicroOp), "the table layout reserves sizeof(MicroOp) per op");
+constexpr int kPostBit = 256;
+
 struct Smem {
-  MicroOp* ops;
+  SOp* ops;
   Exchange* exchanges;
   uint32_t* xbase;
   DiagDesc* diags;
@@ -444,7 +454,7 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
     S.xbuf = xb + (uint32_t)grp * gbuf;
     unsigned char* const p = smem_raw;
     // table offsets come from the host (constant bank): the pointers are then cheap to rematerialise
-    S.ops = reinterpret_cast<MicroOp*>(p + a.off.ops);
+    S.ops = reinterpret_cast<SOp*>(p + a.off.ops);
     S.exchanges = reinterpret_cast<Exchange*>(p + a.off.exch);
     S.xbase = CL ? const_cast<uint32_t*>(a.xbase) : reinterpret_cast<uint32_t*>(p + a.off.xbase);
     S.diags = reinterpret_cast<DiagDesc*>(p + a.off.diags);
@@ -460,8 +470,13 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
     }
     const int tid = threadIdx.x;
     const uint32_t* src; uint32_t* dst; int words;
-    src = reinterpret_cast<const uint32_t*>(a.ops); dst = reinterpret_cast<uint32_t*>(S.ops); words = a.n_ops * (int)(sizeof(MicroOp) / 4);
-    for (int i = tid; i < words; i += blockDim.x) dst[i] = src[i];
+    for (int i = tid; i < a.n_ops; i += blockDim.x) {
+      const MicroOp m = a.ops[i];
+      SOp o;
+      o.h = m.pad0 | ((m.b & kCu3InlinePost) ? kPostBit : 0); o.idx = m.idx; o.acc = m.acc; o.aux = m.aux;
+      o.cf = *reinterpret_cast<const float4*>(a.coef + (size_t)m.pad1 * QNN_COEF_STRIDE);
+      S.ops[i] = o;
+    }
     src = reinterpret_cast<const uint32_t*>(a.exchanges); dst = reinterpret_cast<uint32_t*>(S.exchanges); words = a.n_exchanges * (int)(sizeof(Exchange) / 4);
     for (int i = tid; i < words; i += blockDim.x) dst[i] = src[i];
     if (!CL) for (int i = tid; i < a.n_xbase; i += blockDim.x) S.xbase[i] = a.xbase[i];
@@ -548,30 +563,29 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
     // One jump per micro-op (handler id = kind and register bits); the next op and its coefficient row
     // are fetched while the current body runs, so the dispatch latency overlaps with arithmetic.
     {
-      MicroOp op = S.ops[0];
-      float4 cfa = *reinterpret_cast<const float4*>(S.coef + op.pad1 * 8);
-      for (int pc = 0; op.pad0 != H_END; ++pc) {
-        const MicroOp next = S.ops[pc + 1];
-        const float4 ncfa = *reinterpret_cast<const float4*>(S.coef + next.pad1 * 8);
+      SOp op = S.ops[0];
+      for (int pc = 0; (op.h & 255) != H_END; ++pc) {
+        const SOp next = S.ops[pc + 1];
+        const float4 cfa = op.cf;
         // Handlers with a lane-dependent branch (parity-controlled CU3) may leave the warp split; without this
         // the two halves run the following handlers one after the other until the next exchange (measured: the
         // merged diagonal after a controlled U3 executed twice per warp).
         __syncwarp();
-        switch (op.pad0) {
+        switch (op.h & 255) {
 #define H_CASE_ROT(RB) case H_ROT + RB: rot<RB>(ps, cfa.x, cfa.y); break;
           H_CASE_ROT(0) H_CASE_ROT(1) H_CASE_ROT(2) H_CASE_ROT(3) H_CASE_ROT(4)
 #undef H_CASE_ROT
 #define H_CASE_ROTX(RB) case H_ROTX + RB: { const float2 ab = xc[op.idx]; rot<RB>(ps, ab.x, ab.y); } break;
           H_CASE_ROTX(0) H_CASE_ROTX(1) H_CASE_ROTX(2) H_CASE_ROTX(3) H_CASE_ROTX(4)
 #undef H_CASE_ROTX
-#define H_CASE_CU3L(RT, RC) case H_CU3L + RT * 4 + (RC < RT ? RC : RC - 1): { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_loc<RT, RC>(ps, g, op.b & kCu3InlinePost); } break;
+#define H_CASE_CU3L(RT, RC) case H_CU3L + RT * 4 + (RC < RT ? RC : RC - 1): { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_loc<RT, RC>(ps, g, op.h & kPostBit); } break;
           H_CASE_CU3L(0, 1) H_CASE_CU3L(0, 2) H_CASE_CU3L(0, 3) H_CASE_CU3L(0, 4)
           H_CASE_CU3L(1, 0) H_CASE_CU3L(1, 2) H_CASE_CU3L(1, 3) H_CASE_CU3L(1, 4)
           H_CASE_CU3L(2, 0) H_CASE_CU3L(2, 1) H_CASE_CU3L(2, 3) H_CASE_CU3L(2, 4)
           H_CASE_CU3L(3, 0) H_CASE_CU3L(3, 1) H_CASE_CU3L(3, 2) H_CASE_CU3L(3, 4)
           H_CASE_CU3L(4, 0) H_CASE_CU3L(4, 1) H_CASE_CU3L(4, 2) H_CASE_CU3L(4, 3)
 #undef H_CASE_CU3L
-#define H_CASE_CU3P(RB) case H_CU3P + RB: if (__popc(tis & op.aux) & 1) { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_all<RB>(ps, g, op.b & kCu3InlinePost); } break;
+#define H_CASE_CU3P(RB) case H_CU3P + RB: if (__popc(tis & op.aux) & 1) { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_all<RB>(ps, g, op.h & kPostBit); } break;
           H_CASE_CU3P(0) H_CASE_CU3P(1) H_CASE_CU3P(2) H_CASE_CU3P(3) H_CASE_CU3P(4)
 #undef H_CASE_CU3P
           case H_ROT5: {
@@ -607,7 +621,6 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
           default: break;
         }
         op = next;
-        cfa = ncfa;
       }
     }
     }  // forward program (skipped when the backward pass starts from a saved state)
@@ -680,16 +693,16 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
         for (int j = 0; j < NA; ++j) ls[j] = mul2(cj[j], ps[j]);
       }
       // ================= reverse program =================
-      MicroOp op = S.ops[a.n_ops - 2];
-      float4 cfa = *reinterpret_cast<const float4*>(S.coef + op.pad1 * 8);
       for (int pc = a.n_ops - 2; pc >= 0; --pc) {
-        const MicroOp next = S.ops[pc > 0 ? pc - 1 : 0];
-        const float4 ncfa = *reinterpret_cast<const float4*>(S.coef + next.pad1 * 8);
+        // no prefetch of the next op here: at 255 registers it would travel through local memory anyway
+        // (measured: cfg3 backward 3.37 -> 3.22 ms without it)
+        const SOp op = S.ops[pc];
+        const float4 cfa = op.cf;
         // Handlers with a lane-dependent branch (parity-controlled CU3) may leave the warp split; without this
         // the two halves run the following handlers one after the other until the next exchange (measured: the
         // merged diagonal after a controlled U3 executed twice per warp).
         __syncwarp();
-        switch (op.pad0) {
+        switch (op.h & 255) {
 #define H_CASE_ROT(RB) case H_ROT + RB: { float v = rot_grad<RB>(ps, ls); rot<RB>(ps, -cfa.x, -cfa.y); rot<RB>(ls, -cfa.x, -cfa.y); \
             if (op.acc >= 0) { v = warp_sum(v); if (lane == 0) wacc[op.acc] += v; } } break;
           H_CASE_ROT(0) H_CASE_ROT(1) H_CASE_ROT(2) H_CASE_ROT(3) H_CASE_ROT(4)
@@ -705,7 +718,7 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
               if ((lane & 7) == 0 && (lane >> 3) < 3) wacc[(ACC) + (lane >> 3)] += r;                       \
             }
 #define H_CASE_CU3L(RT, RC) case H_CU3L + RT * 4 + (RC < RT ? RC : RC - 1): { const float2 z = make_float2(0.f, 0.f); Cu3Acc A{z, z, z, z}; \
-            const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), true); cu3_loc_bwd<RT, RC>(ps, ls, g, A, op.b & kCu3InlinePost); CU3_REDUCE(A, op.acc) } break;
+            const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), true); cu3_loc_bwd<RT, RC>(ps, ls, g, A, op.h & kPostBit); CU3_REDUCE(A, op.acc) } break;
           H_CASE_CU3L(0, 1) H_CASE_CU3L(0, 2) H_CASE_CU3L(0, 3) H_CASE_CU3L(0, 4)
           H_CASE_CU3L(1, 0) H_CASE_CU3L(1, 2) H_CASE_CU3L(1, 3) H_CASE_CU3L(1, 4)
           H_CASE_CU3L(2, 0) H_CASE_CU3L(2, 1) H_CASE_CU3L(2, 3) H_CASE_CU3L(2, 4)
@@ -713,7 +726,7 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
           H_CASE_CU3L(4, 0) H_CASE_CU3L(4, 1) H_CASE_CU3L(4, 2) H_CASE_CU3L(4, 3)
 #undef H_CASE_CU3L
 #define H_CASE_CU3P(RB) case H_CU3P + RB: { const float2 z = make_float2(0.f, 0.f); Cu3Acc A{z, z, z, z}; \
-            if (__popc(tis & op.aux) & 1) { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), true); cu3_all_bwd<RB>(ps, ls, g, A, op.b & kCu3InlinePost); } \
+            if (__popc(tis & op.aux) & 1) { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), true); cu3_all_bwd<RB>(ps, ls, g, A, op.h & kPostBit); } \
             CU3_REDUCE(A, op.acc) } break;
           H_CASE_CU3P(0) H_CASE_CU3P(1) H_CASE_CU3P(2) H_CASE_CU3P(3) H_CASE_CU3P(4)
 #undef H_CASE_CU3P
@@ -781,11 +794,11 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
             if ((lane & 1) == 0) {
               const int comp = lane >> 1;
               const int ai = comp < kR ? D->acc_reg[comp]
-                                       : (comp < kR + kMaxThreadBits && op.pad0 == H_DIAG ? D->acc_thr[comp - kR] : -1);
+                                       : (comp < kR + kMaxThreadBits && (op.h & 255) == H_DIAG ? D->acc_thr[comp - kR] : -1);
               if (ai >= 0) wacc[ai] += r;
             }
             __syncwarp();   // reconverge before the table multiply (ptxas otherwise runs it once per lane subset)
-            if (op.pad0 == H_DIAG) diag_mul<true, true>(ps, ls, S.big + (size_t)op.idx * 32 * G, G, tig);
+            if ((op.h & 255) == H_DIAG) diag_mul<true, true>(ps, ls, S.big + (size_t)op.idx * 32 * G, G, tig);
             else diag_mul<true, true>(ps, ls, S.small + op.idx * 32, 1, 0);
           } break;
           case H_XCHG: {   // inverse: roles of the two address sets swapped
@@ -803,8 +816,6 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
           } break;
           default: break;
         }
-        op = next;
-        cfa = ncfa;
       }
       // ================= input gradients of this group's samples =================
       if (AMP) {
