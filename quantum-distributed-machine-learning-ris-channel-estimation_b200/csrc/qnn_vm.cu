@@ -38,7 +38,7 @@ size_t table_bytes(const Program& p, int n_inputs, int warps, bool bwd, bool clu
 // exchange buffers (8 KB per warp, each group's aligned to its size) + worst-case alignment gap + tables;
 // the cluster geometry keeps its exchange buffer in the workspace
 size_t smem_bytes(const Program& p, int n_inputs, int warps, bool bwd, bool cluster) {
-  if (cluster) return table_bytes(p, n_inputs, warps, bwd, true) + 64;
+  if (cluster) return table_bytes(p, n_inputs, warps, bwd, true) + 2 * 65536 + 64;   // + alignment gap + the local-exchange buffer
   const size_t group_buf = (size_t)8192 << p.wb;
   return group_buf + (size_t)warps * 8192 + table_bytes(p, n_inputs, warps, bwd, false) + 64;
 }

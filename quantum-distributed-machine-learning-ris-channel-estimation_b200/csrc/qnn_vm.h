@@ -37,7 +37,7 @@ enum MopKind : int32_t {
   MOP_CU3_P = 5,      // same with control = parity(lane_in_sample & aux)
   MOP_DIAG = 6,       // multiply by diagonal table idx ([j][lane], 1024 entries); desc aux
   MOP_DIAG_REG = 7,   // diagonal that depends on register bits only (32-entry table idx); desc aux
-  MOP_XCHG = 8,       // exchange idx
+  MOP_XCHG = 8,       // exchange idx; aux = 1: local exchange of the cluster geometry (else through L2)
   // macro-ops: one dispatch for a whole group (the per-op dispatch latency is otherwise comparable to a body)
   MOP_ROT5 = 9,       // rotations on all five register bits; bit k uses coef row idx + pos_k and accumulator
                       //   acc + pos_k, pos_k = (aux >> 3k) & 7
@@ -77,7 +77,7 @@ struct DiagDesc {      // per DIAG / DIAG_REG micro-op
 struct Exchange {      // byte offsets into the group's buffer (8 KB per warp); address = base[thread] ^ off[j]
   uint32_t woff[32], roff[32];
   uint32_t base;       // first of 2 * G entries in Program::xbase (G = threads per group): write bases, then read bases
-  uint32_t pad[3];
+  uint32_t pad[3];     // pad[0] = 1: cluster geometry, local exchange (through the CTA's own shared memory)
 };
 
 struct GradSlot {      // gw[weight] += accumulator[acc]  (every gradient is a direct, already-reduced sum)

@@ -82,6 +82,7 @@ struct Builder {
   const qnn_circuit* c;
   Program* P;
   int n, tb;
+  bool no_local = false;   // cluster geometry: never use the shared-memory (local) exchange
   int policy = 0;   // how "apply the pending diagonal" and "exchange" are ordered when both are possible
   std::vector<Item> items;
   uint32_t rowmask[16];
@@ -330,8 +331,39 @@ struct Builder {
     return false;
   }
 
+  // Cluster geometry (n >= 14): bits 13.. of the extended index are the CTA rank.  An exchange that leaves the
+  // wires on those bits where they are moves nothing between SMs and can run through the CTA's own shared
+  // memory ("local"); only when a wanted wire sits on a CTA bit does the state have to cross the L2 ("global").
+  // `global` false: the wanted wires take the register bits, the wires they displace take the vacated bits,
+  // every other clean wire stays.  `global` true: the CTA bits receive the wires that are needed last.
+  void choose_layout_cluster(int* bit_of_wire, const std::vector<int>& order_in, bool global) {
+    std::vector<int> order(order_in.begin(), order_in.begin() + kR);
+    if (global && all_clean())
+      std::stable_partition(order.begin(), order.end(), [&](int w) { const int b = ctz(rowmask[w]); return b >= kR && b < 10; });
+    std::vector<int> nb(n, -1);
+    uint32_t taken = 0;
+    for (int r = 0; r < kR; ++r) { nb[order[r]] = r; taken |= 1u << r; }
+    auto next_use = [&](int w) {
+      for (size_t i = 0; i < items.size(); ++i)
+        if (!items[i].done && (items[i].kind == IT_REAL || items[i].kind == IT_CGEN) && (items[i].w0 == w || items[i].w1 == w))
+          return (int)i;
+      return (int)items.size() + 1;
+    };
+    if (global) {
+      std::vector<int> rest;
+      for (int w = 0; w < n; ++w) if (nb[w] < 0) rest.push_back(w);
+      std::stable_sort(rest.begin(), rest.end(), [&](int a, int b) { return next_use(a) > next_use(b); });
+      for (int k = 0; k < n - 13 && k < (int)rest.size(); ++k) { nb[rest[k]] = 13 + k; taken |= 1u << (13 + k); }
+    }
+    for (int w = 0; w < n; ++w)          // clean wires keep their bit when it is still free
+      if (nb[w] < 0 && clean(w)) { const int b = bit_of(w); if (!((taken >> b) & 1u)) { nb[w] = b; taken |= 1u << b; } }
+    for (int w = 0; w < n; ++w)
+      if (nb[w] < 0) { int b = 0; while ((taken >> b) & 1u) ++b; nb[w] = b; taken |= 1u << b; }
+    for (int w = 0; w < n; ++w) bit_of_wire[w] = nb[w];
+  }
+
   // Wires wanted on register bits next, in order of need.
-  void choose_layout(int* bit_of_wire) {
+  void choose_layout(int* bit_of_wire, bool global = true) {
     std::vector<int> order;
     auto add = [&](int w) { if (w >= 0 && std::find(order.begin(), order.end(), w) == order.end()) order.push_back(w); };
     for (size_t i = 0; i < items.size() && (int)order.size() < kR; ++i) {
@@ -344,10 +376,11 @@ struct Builder {
     for (int w = 0; w < n && (int)order.size() < kR; ++w)
       if (is_unit(rowmask[w]) && ctz(rowmask[w]) < kR) add(w);
     for (int w = 0; w < n && (int)order.size() < kR; ++w) add(w);
-    if (P->wb > 3 && all_clean()) {
-      // cluster geometry: wires that now sit on lane bits take the low register bits, so that after the
-      // exchange a thread's registers 0..3 are consecutive slots of the L2 buffer (one 32-byte sector)
-      std::stable_partition(order.begin(), order.begin() + kR, [&](int w) { const int b = ctz(rowmask[w]); return b >= kR && b < 10; });
+    if (P->wb > 3) {
+      // (global exchanges: wires that now sit on lane bits take the low register bits, so that after the
+      // exchange a thread's registers 0..3 are consecutive slots of the L2 buffer, one 32-byte sector)
+      choose_layout_cluster(bit_of_wire, order, global);
+      return;
     }
     std::vector<bool> used(n, false);
     for (int r = 0; r < kR; ++r) { bit_of_wire[order[r]] = r; used[order[r]] = true; }
@@ -355,7 +388,7 @@ struct Builder {
     for (int w = 0; w < n; ++w) if (!used[w]) bit_of_wire[w] = b++;
   }
 
-  bool emit_exchange(const int* new_bit_of_wire) {
+  bool emit_exchange(const int* new_bit_of_wire, bool allow_global = true, bool* local_out = nullptr) {
     uint32_t inv_col[16];
     if (!invert(rowmask, n, inv_col)) { P->why_not = "internal: singular layout"; return false; }
     // Extended index of an amplitude inside a group's buffer: bits 0..4 register index, 5..9 lane,
@@ -369,11 +402,22 @@ struct Builder {
     // and the reading side are well-behaved: the low slot bits must be a bijection of the lane bits
     Lcg rng{0x9E3779B97F4A7C15ULL + P->exchanges.size() * 7919ULL};
     uint32_t scol[16], rcol[16];
-    const uint32_t emask = (1u << E) - 1u;
+    // cluster geometry: the exchange is local when every new CTA bit is the old one and no other new bit
+    // depends on an old CTA bit - then an amplitude's slot is an address in its own CTA's 64 KB buffer
+    bool local = P->wb > 3 && !no_local;
+    if (local)
+      for (int b = 0; b < E; ++b) {
+        const uint32_t hi = acol[b] >> 13;
+        if (hi != (b >= 13 ? 1u << (b - 13) : 0u)) local = false;
+      }
+    if (local_out) *local_out = local;
+    if (P->wb > 3 && !local && !allow_global) return true;     // caller retries with a global layout
+    const int ES = local ? 13 : E;                             // slot bits
+    const uint32_t emask = (1u << ES) - 1u;
     for (int attempt = 0;; ++attempt) {
       if (attempt > 200000) { P->why_not = "internal: no conflict-free exchange found"; return false; }
-      for (int e = 0; e < E; ++e) scol[e] = rng.next() & emask;
-      if (P->wb > 3) {
+      for (int e = 0; e < E; ++e) scol[e] = e < ES ? (rng.next() & emask) : 0u;
+      if (P->wb > 3 && !local) {
         // L2 buffer: a warp's 32 lanes write one aligned 256-byte block: the low five slot bits are the lane
         // bits.  (A transposition cannot be coalesced on the reading side as well; but when the wires coming
         // onto register bits 0 and 1 were on lane bits, those lane bits become slot bits 0 and 1 and every
@@ -389,13 +433,13 @@ struct Builder {
           if (slot_of_lane[i] < 0) { int b = 0; while ((taken >> b) & 1u) ++b; slot_of_lane[i] = b; taken |= 1u << b; }
         for (int i = 0; i < 5; ++i) scol[5 + i] = 1u << slot_of_lane[i];
       }
-      if (!independent(scol, E)) continue;
+      if (!independent(scol, ES)) continue;
       for (int b = 0; b < E; ++b) {
         uint32_t s = 0;
         for (int e = 0; e < E; ++e) if ((acol[b] >> e) & 1u) s ^= scol[e];
         rcol[b] = s;
       }
-      if (P->wb > 3) break;
+      if (P->wb > 3 && !local) break;
       // shared-memory buffer: no bank conflicts within a half-warp, writing and reading
       uint32_t wlow[4], rlow[4];
       for (int i = 0; i < 4; ++i) { wlow[i] = scol[5 + i] & 15u; rlow[i] = rcol[5 + i] & 15u; }
@@ -415,8 +459,9 @@ struct Builder {
         for (int i = 0; i < 5 + P->wb; ++i) if ((t >> i) & 1) b ^= side ? rcol[5 + i] : scol[5 + i];
         P->xbase.push_back(b * 8);
       }
+    X.pad[0] = local ? 1u : 0u;
     MicroOp m{};
-    m.kind = MOP_XCHG; m.idx = (int)P->exchanges.size(); m.acc = -1;
+    m.kind = MOP_XCHG; m.idx = (int)P->exchanges.size(); m.acc = -1; m.aux = local ? 1 : 0;
     P->exchanges.push_back(X);
     P->ops.push_back(m);
     for (int w = 0; w < n; ++w) rowmask[w] = 1u << new_bit_of_wire[w];
@@ -555,6 +600,12 @@ struct Builder {
       }
       if (flush_first) { flush_diag(); continue; }
       if (b >= 0) {
+        if (P->wb > 3 && !no_local) {          // cluster geometry: a local exchange when it can do the job
+          bool local = false;
+          choose_layout(bits, false);
+          if (!emit_exchange(bits, false, &local)) return false;
+          if (local) continue;
+        }
         choose_layout(bits);
         if (!emit_exchange(bits)) return false;
         continue;
@@ -599,7 +650,7 @@ static double program_cost(const Program& p) {
       case MOP_CU3_P: cost += 6.0; break;
       case MOP_DIAG_REG: cost += 5.0; break;
       case MOP_DIAG: cost += 6.0; break;
-      case MOP_XCHG: cost += 4.6; break;
+      case MOP_XCHG: cost += p.wb > 3 ? (m.aux ? 8.0 : 40.0) : 4.6; break;   // cluster: shared memory vs L2
       default: break;
     }
   }
@@ -611,10 +662,20 @@ void compile(const qnn_circuit* c, Program* out) {
   // each policy and keeping the cheapest program.
   Program best;
   double best_cost = 0;
+  // Cluster geometry: local exchanges need a 64 KB buffer (plus its alignment gap) in every CTA next to the
+  // program's tables; programs whose tables leave no room for it are compiled with L2 exchanges only.
+  for (int no_local = 0; no_local < 2; ++no_local) {
+  if (no_local) {
+    if (!best.ok || best.wb <= 3) break;
+    const size_t tables = best.ops.size() * sizeof(MicroOp) + best.exchanges.size() * sizeof(Exchange) +
+                          best.diags.size() * sizeof(DiagDesc) + best.coef_ops.size() * 32 + (size_t)best.n_small_tables * 256;
+    if (tables <= 80 * 1024) break;
+    best = Program();
+  }
   for (int policy = 0; policy < 3; ++policy) {
     Program cand;
     Builder b{};
-    b.c = c; b.P = &cand; b.policy = policy;
+    b.c = c; b.P = &cand; b.policy = policy; b.no_local = no_local != 0;
     if (!b.run()) {
       cand.ok = false;
       cand.ops.clear();
@@ -623,6 +684,7 @@ void compile(const qnn_circuit* c, Program* out) {
     }
     const double cost = program_cost(cand);
     if (!best.ok || cost < best_cost) { best = cand; best_cost = cost; }
+  }
   }
   *out = best;
 }
@@ -679,7 +741,7 @@ std::string describe(const Program& p) {
     tab("woff", X.woff, 32, false);
     tab("rbase", p.xbase.data() + X.base + G, G, false);
     tab("roff", X.roff, 32, false);
-    o << "}";
+    o << ", \"local\": " << X.pad[0] << "}";
   }
   o << "], \"slots\": [";
   for (size_t i = 0; i < p.slots.size(); ++i) {

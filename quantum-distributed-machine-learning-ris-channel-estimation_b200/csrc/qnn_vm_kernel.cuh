@@ -449,7 +449,7 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
   Smem S;
   {
     const uint32_t s0 = (uint32_t)__cvta_generic_to_shared(smem_raw);
-    const uint32_t gbuf = CL ? 16u : (8192u << wbits);
+    const uint32_t gbuf = CL ? 65536u : (8192u << wbits);   // cluster: one CTA-wide buffer for the local exchanges
     const uint32_t xb = (s0 + a.table_bytes + gbuf - 1u) & ~(gbuf - 1u);
     S.xbuf = xb + (uint32_t)grp * gbuf;
     unsigned char* const p = smem_raw;
@@ -502,6 +502,7 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
       asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
     }
   };
+  auto csync = [&]() { asm volatile("bar.sync 0;" ::: "memory"); };   // this CTA only (local exchanges of a cluster)
   // cluster geometry: four exchange buffers per cluster (two alternating sets of {psi, lam})
   unsigned char* const cbuf = CL ? a.cbuf + ((size_t)cid << (a.n + 5)) : nullptr;
   const size_t cbuf_one = (size_t)1 << (a.n + 3);
@@ -613,9 +614,13 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
           case H_XCHG: {
             const Exchange* X = S.exchanges + op.idx;
             if constexpr (CL) {
-              xpar ^= 1u;
-              unsigned char* b0 = cbuf + (size_t)(2 * xpar) * cbuf_one;
-              exchange_global<false>(ps, ps, b0, b0, S.xbase[X->base + tig], S.xbase[X->base + G + tig], X->woff, X->roff, gsync);
+              if (op.aux) {   // local: the CTA bits stay put, the exchange runs through this CTA's shared memory
+                exchange(ps, S.xbuf | S.xbase[X->base + tig], S.xbuf | S.xbase[X->base + G + tig], X->woff, X->roff, csync);
+              } else {
+                xpar ^= 1u;
+                unsigned char* b0 = cbuf + (size_t)(2 * xpar) * cbuf_one;
+                exchange_global<false>(ps, ps, b0, b0, S.xbase[X->base + tig], S.xbase[X->base + G + tig], X->woff, X->roff, gsync);
+              }
             } else exchange(ps, S.xbuf | S.xbase[X->base + tig], S.xbuf | S.xbase[X->base + G + tig], X->woff, X->roff, gsync);
           } break;
           default: break;
@@ -805,9 +810,14 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
             const Exchange* X = S.exchanges + op.idx;
             if constexpr (CL) {
               const uint32_t wa = S.xbase[X->base + G + tig], ra = S.xbase[X->base + tig];
-              xpar ^= 1u;
-              unsigned char* b0 = cbuf + (size_t)(2 * xpar) * cbuf_one;
-              exchange_global<true>(ps, ls, b0, b0 + cbuf_one, wa, ra, X->roff, X->woff, gsync);
+              if (op.aux) {
+                exchange(ps, S.xbuf | wa, S.xbuf | ra, X->roff, X->woff, csync);
+                exchange(ls, S.xbuf | wa, S.xbuf | ra, X->roff, X->woff, csync);
+              } else {
+                xpar ^= 1u;
+                unsigned char* b0 = cbuf + (size_t)(2 * xpar) * cbuf_one;
+                exchange_global<true>(ps, ls, b0, b0 + cbuf_one, wa, ra, X->roff, X->woff, gsync);
+              }
             } else {
               const uint32_t wa = S.xbuf | S.xbase[X->base + G + tig], ra = S.xbuf | S.xbase[X->base + tig];
               exchange(ps, wa, ra, X->roff, X->woff, gsync);

@@ -49,6 +49,20 @@ def test_multi_warp_samples(n, L):
         _check(qris_b200.u3cu3_circuit(n, 1), seed=n + 1)
 
 
+@pytest.mark.parametrize("n,L,kind", [(14, 2, "u3"), (15, 1, "u3"), (16, 2, "ref")])
+def test_cluster_programs_mix_local_and_global_exchanges(n, L, kind):
+    """n >= 14: exchanges that leave the wires on the CTA-rank bits alone run through the CTA's own shared
+    memory (64 KB, bank-conflict free); only the others cross the L2.  The emulator keeps one buffer per CTA
+    for a local exchange, so an address that would leave the CTA fails the run."""
+    c = qris_b200.u3cu3_circuit(n, L) if kind == "u3" else qris_b200.reference_circuit(n, L)
+    desc, stats = _check(c, seed=n)
+    local = sum(x["local"] for x in desc["exchanges"])
+    assert 0 < local < len(desc["exchanges"])
+    for (k, a, b, idx, acc, aux) in desc["ops"]:
+        if k == 8:
+            assert aux == desc["exchanges"][idx]["local"]
+
+
 @pytest.mark.parametrize("n", [5, 8, 10])
 def test_amplitude_encoder_program(n):
     """The (normalised) input row is the initial state, gathered into the program's initial layout."""

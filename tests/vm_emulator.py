@@ -42,8 +42,8 @@ def _apply_reg(state, U, rbit, lane_mask=None, ctrl_rbit=None):
     state[np.ix_(lanes, j1)] = U[1, 0] * a0 + U[1, 1] * a1
 
 
-def check_conflict_free(base, off, writing=True):
-    if len(base) > 32 * 8:                            # cluster geometry: L2 buffer; writes must be coalesced
+def check_conflict_free(base, off, writing=True, local=False):
+    if len(base) > 32 * 8 and not local:              # cluster geometry: L2 buffer; writes must be coalesced
         if writing:
             for j in range(0, 32, 5):
                 for w0 in range(0, len(base), 32):
@@ -149,18 +149,22 @@ def emulate_forward(desc, x, w):
             stats["diag" if kind == MOP_DIAG else "diag_reg"] += 1
         elif kind == MOP_XCHG:
             X = desc["exchanges"][idx]
-            check_conflict_free(X["wbase"], X["woff"])
-            check_conflict_free(X["rbase"], X["roff"], writing=False)
+            local = bool(X.get("local", 0))          # cluster geometry: through each CTA's own 64 KB buffer
+            assert local == bool(aux) and (not local or G > 256)
+            check_conflict_free(X["wbase"], X["woff"], local=local)
+            check_conflict_free(X["rbase"], X["roff"], writing=False, local=local)
+            size = 65536 if local else 8192 * (G // 32)
+            cta = (lambda l: l // 256) if local else (lambda l: 0)
             buf = {}
             for l in range(G):
                 for jj in range(32):
                     addr = X["wbase"][l] ^ X["woff"][jj]
-                    assert addr % 8 == 0 and 0 <= addr < 8192 * (G // 32) and addr not in buf
-                    buf[addr] = state[l, jj]
+                    assert addr % 8 == 0 and 0 <= addr < size and (cta(l), addr) not in buf
+                    buf[(cta(l), addr)] = state[l, jj]
             new = np.empty_like(state)
             for l in range(G):
                 for jj in range(32):
-                    new[l, jj] = buf[X["rbase"][l] ^ X["roff"][jj]]
+                    new[l, jj] = buf[(cta(l), X["rbase"][l] ^ X["roff"][jj])]
             state = new
             stats["xchg"] += 1
         else:
