@@ -175,6 +175,20 @@ QNN_API int qnn_pruned_adamw_step(float* params, float* grads, float* exp_avg, f
                                   float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
                                   float prune_threshold, unsigned long long* pruned_count, void* cuda_stream);
 
+/* Angle head of the classifier: the last two stages of the reference's `preprocess`
+ * stack, nn.Linear(32*(h/4)*(w/4), n_qubits) + nn.Tanh (Est:161-162), which produce the encoder angles:
+ *   x[b, j] = tanh(bias[j] + sum_k f[b, k] * W[j, k])        f [B, K], W [n, K] (torch's Linear layout), x [B, n]
+ * n <= 16, K <= 4096, n*K <= 49152 (the weight matrix is staged in shared memory). */
+QNN_API int qnn_head_forward(const float* f, const float* W, const float* bias, float* x, int64_t B, int32_t K,
+                             int32_t n, void* cuda_stream);
+/* Its backward from gx = dL/dx and the saved output x: gf [B, K] (may be NULL when the features need no
+ * gradient), gW [n, K], gbias [n]; sums over the batch are two-stage and order-fixed.  The workspace holds the
+ * per-CTA partial sums (qnn_head_workspace_bytes; 0 for shapes outside the limits). */
+QNN_API size_t qnn_head_workspace_bytes(int64_t B, int32_t K, int32_t n);
+QNN_API int qnn_head_backward(const float* f, const float* W, const float* x, const float* gx, float* gf, float* gW,
+                              float* gbias, int64_t B, int32_t K, int32_t n, void* workspace, size_t workspace_bytes,
+                              void* cuda_stream);
+
 /* Measured FP32 FMA throughput of the current device in TFLOP/s (register-resident FMA chains,
  * timed with CUDA events; synchronises).  Used only by bench.py for the roofline denominator. */
 QNN_API int qnn_fp32_peak_probe(int32_t iters, double* tflops, double* sm_clock_mhz_unused);

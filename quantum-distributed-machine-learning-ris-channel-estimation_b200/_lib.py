@@ -62,6 +62,9 @@ SIGNATURES = {
     "qnat_backward_apply": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, _i32, C.POINTER(QnatParams), _vp]),
     "qnn_pruned_adamw_step": (C.c_int, [_vp, _vp, _vp, _vp, _i64, C.c_float, C.c_float, C.c_float, C.c_float,
                                         C.c_float, _i64, C.c_float, _vp, _vp]),
+    "qnn_head_forward": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i32, _i32, _vp]),
+    "qnn_head_workspace_bytes": (_sz, [_i64, _i32, _i32]),
+    "qnn_head_backward": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _vp, _sz, _vp]),
     "qnn_fp32_peak_probe": (C.c_int, [_i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "qnn_last_error": (C.c_char_p, []),
     "qnn_abi_version": (_i32, []),

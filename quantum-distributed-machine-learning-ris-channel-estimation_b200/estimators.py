@@ -11,6 +11,7 @@ import torch
 import torch.nn.functional as F
 from torch import nn
 
+from . import head as _head
 from . import pennylane_shim as qml
 
 
@@ -97,8 +98,16 @@ class QSC_P128(nn.Module):
             nn.Flatten(), nn.Linear(32 * (pilot_hw[0] // 4) * (pilot_hw[1] // 4), n_qubits), nn.Tanh())
         self.classifier = nn.Linear(n_qubits, n_classes)         # Est:165
 
+    def _angles(self, x):
+        """``self.preprocess(x)`` (Est:152-162, 173).  For large CUDA batches its last two stages, Linear +
+        Tanh, run as the fused head kernels with the weights of the unchanged ``preprocess[7]`` module."""
+        lin = self.preprocess[7]
+        if x.is_cuda and x.shape[0] >= _head.MIN_BATCH and _head.supported(lin.in_features, lin.out_features):
+            return _head.linear_tanh(self.preprocess[:7](x), lin.weight, lin.bias)
+        return self.preprocess(x)
+
     def forward(self, x):
-        angles = self.preprocess(x)
+        angles = self._angles(x)
         if self.training and self.use_quantumnat and self.noise_level > 0:
             # Weight-space noise for this forward only (Est:176-196).  The layer snapshots the
             # weights it ran with, so the gradient is taken at the noisy point, as in the reference.

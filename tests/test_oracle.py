@@ -152,3 +152,21 @@ def test_weight_noise_restatement():
     out = QO.weight_noise(w, 0.01, generator=g)
     g2 = torch.Generator().manual_seed(7)
     assert torch.equal(out, 0.01 * torch.randn(3, 6, 2, generator=g2))
+
+
+def test_head_oracle_matches_torch():
+    """The angle head IS runnable reference code (nn.Linear + nn.Tanh, Est:161-162): pin the restatement
+    against torch itself, forward and autograd gradients, in float64."""
+    from oracle import head_oracle
+    torch.manual_seed(11)
+    lin = torch.nn.Linear(256, 6).double()
+    f = torch.randn(19, 256, dtype=torch.float64, requires_grad=True)
+    x = torch.tanh(lin(f))
+    gx = torch.randn_like(x)
+    gf, gW, gb = torch.autograd.grad((x * gx).sum(), [f, lin.weight, lin.bias])
+    xo = head_oracle.head_forward(f.detach().numpy(), lin.weight.detach().numpy(), lin.bias.detach().numpy())
+    np.testing.assert_allclose(xo, x.detach().numpy(), rtol=0, atol=1e-13)
+    gfo, gWo, gbo = head_oracle.head_backward(f.detach().numpy(), lin.weight.detach().numpy(), xo, gx.numpy())
+    np.testing.assert_allclose(gfo, gf.numpy(), rtol=0, atol=1e-12)
+    np.testing.assert_allclose(gWo, gW.numpy(), rtol=0, atol=1e-12)
+    np.testing.assert_allclose(gbo, gb.numpy(), rtol=0, atol=1e-12)
