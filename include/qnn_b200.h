@@ -175,6 +175,15 @@ QNN_API int qnn_pruned_adamw_step(float* params, float* grads, float* exp_avg, f
                                   float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
                                   float prune_threshold, unsigned long long* pruned_count, void* cuda_stream);
 
+/* The same step with the step count kept on the device: *steps_done (int64, device) is the number of steps
+ * taken so far; the kernel derives AdamW's bias corrections from it and a second one-thread kernel
+ * increments it.  No argument changes from one step to the next, so a training step that ends with this
+ * call can be recorded once and replayed (what runner.GraphedQSCStep does with a CUDA graph). */
+QNN_API int qnn_pruned_adamw_step_counted(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
+                                          float lr, float beta1, float beta2, float eps, float weight_decay,
+                                          long long* steps_done, float prune_threshold,
+                                          unsigned long long* pruned_count, void* cuda_stream);
+
 /* Angle head of the classifier: the last two stages of the reference's `preprocess`
  * stack, nn.Linear(32*(h/4)*(w/4), n_qubits) + nn.Tanh (Est:161-162), which produce the encoder angles:
  *   x[b, j] = tanh(bias[j] + sum_k f[b, k] * W[j, k])        f [B, K], W [n, K] (torch's Linear layout), x [B, n]

@@ -62,6 +62,8 @@ SIGNATURES = {
     "qnat_backward_apply": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _vp, _i64, _i32, C.POINTER(QnatParams), _vp]),
     "qnn_pruned_adamw_step": (C.c_int, [_vp, _vp, _vp, _vp, _i64, C.c_float, C.c_float, C.c_float, C.c_float,
                                         C.c_float, _i64, C.c_float, _vp, _vp]),
+    "qnn_pruned_adamw_step_counted": (C.c_int, [_vp, _vp, _vp, _vp, _i64, C.c_float, C.c_float, C.c_float, C.c_float,
+                                                C.c_float, _vp, C.c_float, _vp, _vp]),
     "qnn_head_forward": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i32, _i32, _vp]),
     "qnn_head_workspace_bytes": (_sz, [_i64, _i32, _i32]),
     "qnn_head_backward": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _vp, _sz, _vp]),

@@ -20,7 +20,13 @@ namespace {
 __global__ void __launch_bounds__(256) k_pruned_adamw(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
                                                       float* __restrict__ v, long long n, float lr, float b1, float b2,
                                                       float eps, float wd, float step_size, float bc2_sqrt,
-                                                      float threshold, unsigned long long* __restrict__ pruned) {
+                                                      float threshold, unsigned long long* __restrict__ pruned,
+                                                      const long long* __restrict__ steps_done) {
+  if (steps_done != nullptr) {   // step count kept on the device: the bias corrections are computed here
+    const double t = (double)(*steps_done + 1);
+    step_size = (float)((double)lr / (1.0 - pow((double)b1, t)));
+    bc2_sqrt = (float)sqrt(1.0 - pow((double)b2, t));
+  }
   unsigned int local = 0;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     float gi = g[i];
@@ -37,7 +43,24 @@ __global__ void __launch_bounds__(256) k_pruned_adamw(float* __restrict__ p, flo
     if ((threadIdx.x & 31) == 0 && local) atomicAdd(pruned, (unsigned long long)local);   // integer: order-free
   }
 }
+__global__ void k_count_step(long long* steps_done) { *steps_done += 1; }
 }  // namespace
+
+extern "C" int qnn_pruned_adamw_step_counted(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
+                                             float lr, float beta1, float beta2, float eps, float weight_decay,
+                                             long long* steps_done, float prune_threshold,
+                                             unsigned long long* pruned_count, void* cuda_stream) {
+  if (!params || !grads || !exp_avg || !exp_avg_sq || !steps_done) { qnn_set_error("qnn_pruned_adamw_step_counted: NULL buffer"); return QNN_ERR_INVALID; }
+  if (n <= 0) { qnn_set_error("qnn_pruned_adamw_step_counted: n=%lld must be positive", (long long)n); return QNN_ERR_INVALID; }
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, 148 * 8));
+  k_pruned_adamw<<<grid, 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, 0.f, 1.f,
+                                       prune_threshold, pruned_count, steps_done);
+  QNN_CUDA_CHECK(cudaGetLastError());
+  k_count_step<<<1, 1, 0, st>>>(steps_done);
+  QNN_CUDA_CHECK(cudaGetLastError());
+  return QNN_OK;
+}
 
 extern "C" int qnn_pruned_adamw_step(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t n,
                                      float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
@@ -49,7 +72,7 @@ extern "C" int qnn_pruned_adamw_step(float* params, float* grads, float* exp_avg
   const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, 148 * 8));
   k_pruned_adamw<<<grid, 256, 0, static_cast<cudaStream_t>(cuda_stream)>>>(params, grads, exp_avg, exp_avg_sq, n, lr, beta1,
                                                                            beta2, eps, weight_decay, step_size, bc2_sqrt,
-                                                                           prune_threshold, pruned_count);
+                                                                           prune_threshold, pruned_count, nullptr);
   QNN_CUDA_CHECK(cudaGetLastError());
   return QNN_OK;
 }

@@ -23,7 +23,8 @@ class FlatPrunedAdamW:
     """
 
     def __init__(self, params: Iterable[torch.nn.Parameter], lr=1e-3, betas=(0.9, 0.999), eps=1e-8,
-                 weight_decay=0.01, prune_threshold: Optional[float] = None, process_group=None):
+                 weight_decay=0.01, prune_threshold: Optional[float] = None, process_group=None,
+                 device_step_count: bool = False):
         self.params = [p for p in params if p.requires_grad]
         if not self.params or not self.params[0].is_cuda:
             raise _lib.QnnError("FlatPrunedAdamW needs CUDA parameters (its step is a CUDA kernel; no CPU fallback)")
@@ -41,6 +42,9 @@ class FlatPrunedAdamW:
         self.prune_threshold = prune_threshold
         self.process_group = process_group
         self.t = 0
+        # step count on the device: no argument of step() changes between steps, so a whole training step can
+        # be recorded into a CUDA graph and replayed (runner.GraphedQSCStep)
+        self.steps_done = torch.zeros(1, dtype=torch.int64, device=dev) if device_step_count else None
 
     def zero_grad(self) -> None:
         self.bucket.zero()
@@ -50,6 +54,14 @@ class FlatPrunedAdamW:
         self.t += 1
         dev = self.flat.device.index
         thr = -1.0 if self.prune_threshold is None else float(self.prune_threshold)
+        if self.steps_done is not None:
+            with torch.cuda.device(dev):
+                rc = _lib.lib().qnn_pruned_adamw_step_counted(
+                    self.flat.data_ptr(), self.bucket.flat.data_ptr(), self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(),
+                    self.flat.numel(), self.lr, self.betas[0], self.betas[1], self.eps, self.weight_decay,
+                    self.steps_done.data_ptr(), thr, self.pruned.data_ptr(), torch.cuda.current_stream(dev).cuda_stream)
+            _lib.check(rc, "qnn_pruned_adamw_step_counted")
+            return
         with torch.cuda.device(dev):
             rc = _lib.lib().qnn_pruned_adamw_step(
                 self.flat.data_ptr(), self.bucket.flat.data_ptr(), self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(),
@@ -59,4 +71,5 @@ class FlatPrunedAdamW:
 
     def pruned_fraction(self) -> float:
         """Pruned entries / all entries since construction (one device -> host read)."""
-        return float(self.pruned.item()) / max(1, self.t * self.flat.numel())
+        steps = self.t if self.steps_done is None else int(self.steps_done.item())   # replays do not pass through step()
+        return float(self.pruned.item()) / max(1, steps * self.flat.numel())

@@ -24,6 +24,62 @@ from .estimators import Conv_P128, FC_P128, NMSELoss, QSC_P128, SC_P128
 from .optim import FlatPrunedAdamW
 
 
+class GraphedQSCStep:
+    """One optimiser step of the scenario classifier (``Y2HRunner.qsc_step``) as a CUDA graph.
+
+    At the reference's sizes (nine batches of 256, 6 qubits) a step is about a hundred small kernels and is
+    bound by launch and Python overhead, not by the GPU.  The first ``warmup`` calls run eagerly (they are
+    real training steps); the next call records the step - batch copied into fixed input buffers, nine
+    forwards, backward into the flat gradient bucket, pruning + AdamW with its step count on the device -
+    and every later call copies its batch into the same buffers and replays the recording.  A batch of a
+    different shape (the last, shorter one of an epoch) runs eagerly.  Single process only: the gradient
+    all-reduce of a multi-GPU run is not recorded.
+    """
+
+    def __init__(self, runner, model, opt, concat_users: bool = False, warmup: int = 3):
+        if opt.steps_done is None:
+            raise ValueError("GraphedQSCStep needs FlatPrunedAdamW(device_step_count=True)")
+        self.runner, self.model, self.opt, self.concat = runner, model, opt, concat_users
+        self.warmup, self.calls = warmup, 0
+        self.static = None          # fixed input buffers [sid][uid] -> tuple of tensors
+        self.graph = None
+        self.loss = None
+        self.stream = torch.cuda.Stream(device=runner.device)
+
+    def _shapes(self, sutd):
+        return [tuple((t.shape, t.dtype) for t in sutd[s][u]) for s in range(3) for u in range(3)]
+
+    def _load(self, sutd):
+        for s in range(3):
+            for u in range(3):
+                for dst, src in zip(self.static[s][u], sutd[s][u]):
+                    dst.copy_(src)
+
+    def __call__(self, sutd):
+        self.calls += 1
+        if self.static is not None and self._shapes(sutd) != self._shapes(self.static):
+            return self.runner.qsc_step(self.model, self.opt, sutd, self.concat)       # ragged batch: eager
+        if self.static is None:
+            self.static = [[tuple(t.clone() for t in sutd[s][u]) for u in range(3)] for s in range(3)]
+        self._load(sutd)
+        if self.graph is not None:
+            self.graph.replay()
+            return self.loss
+        if self.calls <= self.warmup:
+            # eager steps on the side stream the recording will use (allocator and library warm-up)
+            self.stream.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self.stream):
+                loss = self.runner.qsc_step(self.model, self.opt, self.static, self.concat)
+            torch.cuda.current_stream().wait_stream(self.stream)
+            return loss
+        self.graph = torch.cuda.CUDAGraph()
+        self.stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.graph(self.graph, stream=self.stream):
+            self.loss = self.runner.qsc_step(self.model, self.opt, self.static, self.concat)
+        self.graph.replay()          # recording does not execute: run the step it recorded
+        return self.loss
+
+
 class Y2HRunner:
     def __init__(self, Pilot_num=128, data_len=20000, SNRdb=10, batch_size_DML=256, lr=1e-3, n_epochs=100,
                  device=None, seed=0, workdir="./workspace", n_qubits=6, n_layers=3, verbose=True):
@@ -79,13 +135,19 @@ class Y2HRunner:
         return loss.detach()
 
     def train_QSC_P128(self, n_epochs: Optional[int] = None, use_quantumnat=False, use_gradient_pruning=False,
-                       max_iters_per_epoch: Optional[int] = None, save=True, concat_users=False) -> Dict[str, list]:
+                       max_iters_per_epoch: Optional[int] = None, save=True, concat_users=False,
+                       cuda_graph=False) -> Dict[str, list]:
+        """``cuda_graph``: record one optimiser step (nine forwards, backward, prune + AdamW) into a CUDA graph
+        after three eager steps and replay it for every later batch of the same shape (single process only;
+        see ``GraphedQSCStep``)."""
         torch.manual_seed(self.seed)
         model = QSC_P128(n_qubits=self.n_qubits, n_layers=self.n_layers, use_quantumnat=use_quantumnat,
                          use_gradient_pruning=use_gradient_pruning,
                          pilot_hw=D.pilot_shape(self.Pilot_num)).to(self.device)       # Run:313-316
         opt = FlatPrunedAdamW(model.parameters(), lr=self.lr, weight_decay=0.01,        # Run:320
-                              prune_threshold=model.gradient_threshold if use_gradient_pruning else None)
+                              prune_threshold=model.gradient_threshold if use_gradient_pruning else None,
+                              device_step_count=bool(cuda_graph))
+        graphed = GraphedQSCStep(self, model, opt, concat_users) if cuda_graph and self.world == 1 else None
         train_loader, val_loader = self.get_dataloader_DML()
         self.log("Data Loaded for QSC with QuantumNAT + On-chip QNN optimization!")
         best_acc, t0 = 0.0, time.time()
@@ -97,7 +159,7 @@ class Y2HRunner:
             for it, sutd in enumerate(train_loader):
                 if max_iters_per_epoch is not None and it >= max_iters_per_epoch:
                     break
-                epoch_loss += self.qsc_step(model, opt, sutd, concat_users)
+                epoch_loss += graphed(sutd) if graphed is not None else self.qsc_step(model, opt, sutd, concat_users)
                 n_batches += 1
             avg = float(epoch_loss.item()) / max(n_batches, 1)          # one device->host read per epoch
             self.train_QSC_losses.append(avg)

@@ -101,6 +101,51 @@ def test_short_training_run_learns_and_saves(tmp_path):
     E.QSC_P128().load_state_dict(sd)                     # reference-compatible keys
 
 
+@pytest.mark.parametrize("concat", [False, True])
+def test_graph_replayed_training_steps_match_eager_steps(concat):
+    """runner.GraphedQSCStep: three eager steps, one recorded, the rest replayed - the parameters after eight
+    steps equal those of eight eager steps on the same batches (same kernels, same order; cuDNN's convolution
+    backward is the only non-bit-exact part)."""
+    r = runner.Y2HRunner(data_len=1280, batch_size_DML=128, device="cuda", verbose=False)
+    loader, _ = r.get_dataloader_DML()
+    batches = list(loader)[:8]
+    assert len(batches) == 8
+    finals, losses = [], []
+    for graphed in (False, True):
+        torch.manual_seed(5)
+        model = E.QSC_P128(use_quantumnat=False, use_gradient_pruning=True).cuda().train()
+        opt = optim.FlatPrunedAdamW(model.parameters(), lr=2e-3, weight_decay=0.01, prune_threshold=1e-3,
+                                    device_step_count=True)
+        step = runner.GraphedQSCStep(r, model, opt, concat) if graphed else (lambda b: r.qsc_step(model, opt, b, concat))
+        ls = [float(step(b)) for b in batches]
+        if graphed:
+            assert step.graph is not None and step.calls == 8
+        assert int(opt.steps_done.item()) == 8
+        finals.append(opt.flat.clone()); losses.append(ls)
+    assert np.allclose(losses[0], losses[1], rtol=1e-4, atol=1e-5)
+    scale = float(finals[0].abs().max())
+    assert float((finals[0] - finals[1]).abs().max()) <= 2e-5 * scale
+
+
+def test_device_step_count_matches_host_step_count():
+    """qnn_pruned_adamw_step_counted derives the bias corrections from the device counter: same parameters
+    as qnn_pruned_adamw_step given the step number from the host."""
+    torch.manual_seed(0)
+    ps = [[torch.nn.Parameter(torch.randn(257, device="cuda")), torch.nn.Parameter(torch.randn(3, 5, device="cuda"))] for _ in range(2)]
+    ps[1][0].data.copy_(ps[0][0].data); ps[1][1].data.copy_(ps[0][1].data)
+    opts = [optim.FlatPrunedAdamW(ps[0], lr=1e-2, prune_threshold=0.05), optim.FlatPrunedAdamW(ps[1], lr=1e-2, prune_threshold=0.05, device_step_count=True)]
+    for it in range(7):
+        g = [torch.randn(257, device="cuda"), torch.randn(3, 5, device="cuda")]
+        for o, pp in zip(opts, ps):
+            o.zero_grad()
+            for p, gi in zip(pp, g):
+                p.grad.add_(gi)
+            o.step()
+    assert int(opts[1].steps_done.item()) == 7
+    assert float((opts[0].flat - opts[1].flat).abs().max()) <= 2e-6
+    assert abs(opts[0].pruned_fraction() - opts[1].pruned_fraction()) < 1e-12
+
+
 def test_routed_nmse_parity_kernel_vs_oracle():
     """BASELINE config 5's criterion at small scale: estimator NMSE with the kernel-backed quantum
     classifier within 0.05 dB of the same pipeline driven by the oracle, identical argmax."""
