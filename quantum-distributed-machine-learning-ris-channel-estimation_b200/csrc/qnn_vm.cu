@@ -38,7 +38,11 @@ size_t table_bytes(const Program& p, int n_inputs, int warps, bool bwd, bool clu
 // exchange buffers (8 KB per warp, each group's aligned to its size) + worst-case alignment gap + tables;
 // the cluster geometry keeps its exchange buffer in the workspace
 size_t smem_bytes(const Program& p, int n_inputs, int warps, bool bwd, bool cluster) {
-  if (cluster) return table_bytes(p, n_inputs, warps, bwd, true) + 2 * 65536 + 64;   // + alignment gap + the local-exchange buffer
+  if (cluster) {   // + alignment gap + the 64 KB buffer of the local exchanges, when the program has any
+    bool has_local = false;
+    for (const Exchange& X : p.exchanges) has_local = has_local || X.pad[0] != 0;
+    return table_bytes(p, n_inputs, warps, bwd, true) + (has_local ? 2 * 65536 : 0) + 64;
+  }
   const size_t group_buf = (size_t)8192 << p.wb;
   return group_buf + (size_t)warps * 8192 + table_bytes(p, n_inputs, warps, bwd, false) + 64;
 }

@@ -667,9 +667,12 @@ void compile(const qnn_circuit* c, Program* out) {
   for (int no_local = 0; no_local < 2; ++no_local) {
   if (no_local) {
     if (!best.ok || best.wb <= 3) break;
+    // backward kernel's tables (qnn_vm.cu: table_layout): program, maps, coefficient rows, small diagonal
+    // tables, and eight per-warp copies of the gradient accumulators; 4 KB for the small per-warp scratch
     const size_t tables = best.ops.size() * sizeof(MicroOp) + best.exchanges.size() * sizeof(Exchange) +
-                          best.diags.size() * sizeof(DiagDesc) + best.coef_ops.size() * 32 + (size_t)best.n_small_tables * 256;
-    if (tables <= 80 * 1024) break;
+                          best.diags.size() * sizeof(DiagDesc) + best.coef_ops.size() * 32 + (size_t)best.n_small_tables * 256 +
+                          (size_t)best.n_acc * 32 + 4096;
+    if (tables + 2 * 65536 + 64 <= 227 * 1024) break;
     best = Program();
   }
   for (int policy = 0; policy < 3; ++policy) {

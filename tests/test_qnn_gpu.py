@@ -78,6 +78,19 @@ def test_largest_sizes(n, B):
     check_against_oracle(circ, B, seed=n)
 
 
+def test_deep_cluster_circuit_falls_back_to_l2_exchanges():
+    """Programs whose tables leave no room for the 64 KB local-exchange buffer are compiled with L2
+    exchanges only and still run on the VM."""
+    c = qris_b200.u3cu3_circuit(14, 20)
+    d = c.describe()
+    assert d["ok"] and sum(x["local"] for x in d["exchanges"]) == 0
+    assert _plan(c, 2) == "vm-register"
+    check_against_oracle(c, 2, seed=7)
+    # just below the switch: local exchanges are used and the program still fits
+    c16 = qris_b200.u3cu3_circuit(14, 16)
+    assert sum(x["local"] for x in c16.describe()["exchanges"]) > 0 and _plan(c16, 2) == "vm-register"
+
+
 def test_largest_sizes_generic_family(monkeypatch):
     monkeypatch.setenv("QNN_DISABLE_VM", "1")
     for n, B in ((14, 2), (16, 1)):
