@@ -43,6 +43,8 @@ def launches(path):
     tot = sum(a[1] for a in agg.values())
     print(f"# per-kernel device time from `ncu --metrics gpu__time_duration.sum --clock-control none` ({path})")
     print("# cold-cache, serialised launches: compare SHARES, not absolutes")
+    print("# k_fma_probe is bench.py's FP32 peak probe (roofline denominator); it runs outside the timed steps -\n"
+          "# within a step the backward kernel's share is bwd / (bwd + fwd + the small kernels)")
     print(f"{'share':>7} {'launches':>8} {'total_us':>12} {'avg_us':>10}  kernel")
     for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
         print(f"{a[1] / tot * 100:6.2f}% {a[0]:8d} {a[1]:12.1f} {a[1] / a[0]:10.1f}  {k[:110]}")
