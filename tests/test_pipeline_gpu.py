@@ -127,6 +127,18 @@ def test_graph_replayed_training_steps_match_eager_steps(concat):
     assert float((finals[0] - finals[1]).abs().max()) <= 2e-5 * scale
 
 
+def test_graphed_training_run_with_weight_noise_learns_like_the_eager_run():
+    """train_QSC_P128(cuda_graph=True) with the QuantumNAT weight noise (torch's RNG inside the recording): the
+    loss curve equals the eager run's; the last (shorter) batch of an epoch runs eagerly.  (With the
+    reference's pruning threshold of 0.1 neither run learns - every gradient entry is below it.)"""
+    hists = []
+    for graph in (False, True):
+        r = runner.Y2HRunner(data_len=1500, batch_size_DML=64, n_epochs=3, lr=5e-3, device="cuda", verbose=False)
+        hists.append(r.train_QSC_P128(use_quantumnat=True, use_gradient_pruning=False, cuda_graph=graph, save=False))
+    assert np.allclose(hists[0]["train_loss"], hists[1]["train_loss"], rtol=2e-3)
+    assert hists[1]["train_loss"][-1] < hists[1]["train_loss"][0] and hists[1]["val_acc"][-1] > 0.6
+
+
 def test_device_step_count_matches_host_step_count():
     """qnn_pruned_adamw_step_counted derives the bias corrections from the device counter: same parameters
     as qnn_pruned_adamw_step given the step number from the host."""
