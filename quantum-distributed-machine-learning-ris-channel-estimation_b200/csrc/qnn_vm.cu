@@ -17,7 +17,7 @@ TableLayout table_layout(const Program& p, int n_inputs, int warps, bool bwd, bo
   TableLayout t{};
   t.ops = take(p.ops.size() * sizeof(MicroOp));
   t.exch = take(p.exchanges.size() * sizeof(Exchange));
-  t.xbase = cluster ? 0u : take(p.xbase.size() * sizeof(uint32_t));
+  t.xbase = (cluster || p.wb > 0) ? 0u : take(p.xbase.size() * sizeof(uint32_t));   // n > 10: read from global memory
   t.diags = take(p.diags.size() * sizeof(DiagDesc));
   t.coef = take(p.coef_ops.size() * 8 * sizeof(float));
   align256();

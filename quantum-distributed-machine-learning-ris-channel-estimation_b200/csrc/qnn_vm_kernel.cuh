@@ -456,7 +456,9 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
     // table offsets come from the host (constant bank): the pointers are then cheap to rematerialise
     S.ops = reinterpret_cast<SOp*>(p + a.off.ops);
     S.exchanges = reinterpret_cast<Exchange*>(p + a.off.exch);
-    S.xbase = CL ? const_cast<uint32_t*>(a.xbase) : reinterpret_cast<uint32_t*>(p + a.off.xbase);
+    // n > 10: the per-thread bases (2 * group threads words per exchange, the same for every sample) stay in
+    // global memory - two L1-resident loads per exchange instead of up to 27 KB of shared memory
+    S.xbase = MW ? const_cast<uint32_t*>(a.xbase) : reinterpret_cast<uint32_t*>(p + a.off.xbase);
     S.diags = reinterpret_cast<DiagDesc*>(p + a.off.diags);
     S.coef = reinterpret_cast<float*>(p + a.off.coef);
     float2* sbig = wbits == 0 ? reinterpret_cast<float2*>(p + a.off.big) : nullptr;
@@ -479,7 +481,7 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
     }
     src = reinterpret_cast<const uint32_t*>(a.exchanges); dst = reinterpret_cast<uint32_t*>(S.exchanges); words = a.n_exchanges * (int)(sizeof(Exchange) / 4);
     for (int i = tid; i < words; i += blockDim.x) dst[i] = src[i];
-    if (!CL) for (int i = tid; i < a.n_xbase; i += blockDim.x) S.xbase[i] = a.xbase[i];
+    if (!MW) for (int i = tid; i < a.n_xbase; i += blockDim.x) S.xbase[i] = a.xbase[i];
     src = reinterpret_cast<const uint32_t*>(a.diags); dst = reinterpret_cast<uint32_t*>(S.diags); words = a.n_diags * (int)(sizeof(DiagDesc) / 4);
     for (int i = tid; i < words; i += blockDim.x) dst[i] = src[i];
     for (int i = tid; i < a.n_coef * 8; i += blockDim.x) S.coef[i] = a.coef[(size_t)(i >> 3) * QNN_COEF_STRIDE + (i & 7)];
