@@ -38,6 +38,8 @@ WORKLOADS = {
     "cfg2": ("ref", 6, 3, 4096, False,
              "BASELINE configs[1]: reference RY/RZ/CNOT circuit n=6 L=3 (P=128 pipeline's QNN), batch 4096 per GPU"),
     "ref10": ("ref", 10, 3, 65536, False, "reference RY/RZ/CNOT circuit at n=10 L=3, batch 65536 per GPU"),
+    "cfg4": ("u3cu3", 16, 8, 576, False,
+             "BASELINE configs[3]: 16-qubit U3+CU3 L=8 (a sample spans a cluster of 8 CTAs), adjoint backward, batch 576 per GPU"),
 }
 
 
