@@ -13,7 +13,8 @@
  *    global state between calls (several forwards may be outstanding before one backward,
  *    Run:341-364);
  *  - all work is enqueued on `cuda_stream` (a cudaStream_t); no call synchronises the device;
- *  - the device is the one current on the calling thread (the caller's tensors live there);
+ *  - the device is the one current on the calling thread (the caller's tensors live there); it must be
+ *    the device that was current when the circuit was created (its tables live there), else QNN_ERR_INVALID;
  *  - wire 0 is the most significant bit of the basis index (PennyLane's convention);
  *  - B may be any positive value.
  */
@@ -75,6 +76,12 @@ typedef struct qnn_circuit qnn_circuit; /* immutable after creation; shareable a
  * n_inputs = row length of x; n_weights = length of w. */
 QNN_API int qnn_circuit_create(const qnn_op* ops, int32_t n_ops, int32_t n_qubits, int32_t n_inputs,
                        int32_t n_weights, int32_t encoder, qnn_circuit** out);
+/* Same, with creation flags.  QNN_CREATE_GENERIC_ONLY keeps the circuit on the generic (shared-memory
+ * interpreter) kernel family even where the register-resident family applies; the parity tests use it to
+ * check one family against the other.  No counterpart in the reference. */
+#define QNN_CREATE_GENERIC_ONLY 1u
+QNN_API int qnn_circuit_create_ex(const qnn_op* ops, int32_t n_ops, int32_t n_qubits, int32_t n_inputs,
+                                  int32_t n_weights, int32_t encoder, uint32_t flags, qnn_circuit** out);
 QNN_API void qnn_circuit_destroy(qnn_circuit* c);
 
 /* Introspection. */
@@ -123,7 +130,9 @@ QNN_API int qnn_backward_saved(const qnn_circuit* c, const float* x, const float
                                const float* state, float* gx, float* gw, int64_t B, void* workspace,
                                size_t workspace_bytes, void* cuda_stream);
 
-/* No counterpart in the reference.  Same result as qnn_backward, for callers that cannot supply a
+/* No counterpart in the reference.  Same gradients as qnn_backward (always computed by the generic kernel
+ * family, so for n = 5..16 they agree with qnn_backward's register-resident kernels to rounding, not bit for
+ * bit, and take several times longer), for callers that cannot supply a
  * workspace because they may not allocate device memory once running: real-time loops (a per-slot
  * channel-estimation service) where cudaMalloc's device-wide synchronisation and unbounded latency
  * are not acceptable, processes whose HBM is owned in full by another pool so that cudaMalloc
@@ -154,14 +163,16 @@ QNN_API size_t qnat_workspace_bytes(int64_t B, int32_t n);
 /* stage 1: per-qubit [sum y, sum y^2] over this rank's B rows -> sums [2*n] doubles (device). */
 QNN_API int qnat_batch_sums(const float* y, double* sums, int64_t B, int32_t n, void* workspace,
                     size_t workspace_bytes, void* cuda_stream);
-/* stage 2: apply; sums as produced by stage 1 (possibly all-reduced), B_total the row count they cover. */
+/* stage 2: apply; sums as produced by stage 1 (possibly all-reduced), B_total the row count they cover.
+ * B_total = 0: the count is read on the device from sums[2*n] (a double the caller keeps next to the sums and
+ * all-reduces with them), so ranks with unequal shard sizes need no host round trip to learn the global count. */
 QNN_API int qnat_apply(const float* y, const float* noise, const double* sums, int64_t B_total, float* out,
                float* yn, float* stats, int64_t B, int32_t n, const qnat_params* p, void* cuda_stream);
 /* backward stage 1: per-qubit [sum g, sum g*yh] with g = STE-masked gout -> bsums [2*n] doubles. */
 QNN_API int qnat_backward_sums(const float* gout, const float* y, const float* yn, const float* stats,
                        double* bsums, int64_t B, int32_t n, const qnat_params* p, void* workspace,
                        size_t workspace_bytes, void* cuda_stream);
-/* backward stage 2: gy = rstd * (g - s1/B_total - yh * s2/(B_total-1)). */
+/* backward stage 2: gy = rstd * (g - s1/B_total - yh * s2/(B_total-1)).  B_total = 0: read from bsums[2*n]. */
 QNN_API int qnat_backward_apply(const float* gout, const float* y, const float* yn, const float* stats,
                         const double* bsums, int64_t B_total, float* gy, int64_t B, int32_t n,
                         const qnat_params* p, void* cuda_stream);

@@ -25,7 +25,16 @@ METRICS = [
     "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
     "smsp__sass_thread_inst_executed_op_ffma_pred_on.sum", "smsp__sass_thread_inst_executed_op_fmul_pred_on.sum",
     "smsp__sass_thread_inst_executed_op_fadd_pred_on.sum",
+    "lts__t_bytes.sum", "lts__t_sectors_op_read.sum", "lts__t_sectors_op_write.sum",
+    "lts__t_sectors_srcunit_tex_op_read.sum", "lts__t_sectors_srcunit_tex_op_write.sum",
+    "lts__throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed",
+    "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum", "l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum",
+    "l1tex__t_sectors_pipe_lsu_mem_global_op_st.sum", "l1tex__t_requests_pipe_lsu_mem_global_op_st.sum",
+    "launch__cluster_size", "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem",
 ]
+# every warp-stall reason as a share of the issue-stalled samples (names differ a little between ncu versions)
+STALL_PATTERNS = ("smsp__average_warp_latency_issue_stalled", "smsp__average_warps_issue_stalled",
+                  "smsp__warp_issue_stalled", "smsp__pcsamp_warps_issue_stalled")
 
 
 def launches(path):
@@ -61,6 +70,16 @@ def full(path):
         for m in METRICS:
             if m in idx:
                 print(f"{m:85s} {r[idx[m]]:>18s} {units[idx[m]]}")
+        stalls = []
+        for h in hdr:
+            if h.startswith(STALL_PATTERNS) and (h.endswith(".pct") or h.endswith(".ratio") or "pcsamp" in h):
+                try:
+                    stalls.append((float(r[idx[h]].replace(",", "")), h))
+                except ValueError:
+                    pass
+        for v, h in sorted(stalls, reverse=True)[:14]:
+            if v > 0:
+                print(f"{h:85s} {v:18.4f} {units[idx[h]]}")
 
 
 if __name__ == "__main__":

@@ -16,6 +16,7 @@ SRC_CONST = -(2 ** 31)
 GATE = {"RX": 0, "RY": 1, "RZ": 2, "U3": 3, "CNOT": 4, "CZ": 5, "CU3": 6}
 GATE_ANGLES = {"RX": 1, "RY": 1, "RZ": 1, "U3": 3, "CNOT": 0, "CZ": 0, "CU3": 3}
 ENCODER = {"none": 0, "amplitude": 1}
+CREATE_GENERIC_ONLY = 1   # qnn_circuit_create_ex flag
 
 
 class QnnOp(C.Structure):
@@ -38,6 +39,7 @@ _vp, _i32, _i64, _sz = C.c_void_p, C.c_int32, C.c_int64, C.c_size_t
 # name -> (restype, argtypes); mirrors include/qnn_b200.h one to one (tests check the export list).
 SIGNATURES = {
     "qnn_circuit_create": (C.c_int, [C.POINTER(QnnOp), _i32, _i32, _i32, _i32, _i32, C.POINTER(_vp)]),
+    "qnn_circuit_create_ex": (C.c_int, [C.POINTER(QnnOp), _i32, _i32, _i32, _i32, _i32, C.c_uint32, C.POINTER(_vp)]),
     "qnn_circuit_destroy": (None, [_vp]),
     "qnn_circuit_n_qubits": (_i32, [_vp]),
     "qnn_circuit_n_inputs": (_i32, [_vp]),

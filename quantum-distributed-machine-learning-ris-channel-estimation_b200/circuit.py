@@ -28,13 +28,16 @@ class Circuit:
     """Immutable gate list + lazily created device handles (one per CUDA device)."""
 
     def __init__(self, n_qubits: int, ops: Sequence[Op], n_inputs: int, n_weights: int,
-                 encoder: str = "none"):
+                 encoder: str = "none", generic_only: bool = False):
         if encoder not in _lib.ENCODER:
             raise ValueError(f"encoder must be one of {sorted(_lib.ENCODER)}, got {encoder!r}")
         self.n_qubits = int(n_qubits)
         self.n_inputs = int(n_inputs)
         self.n_weights = int(n_weights)
         self.encoder = encoder
+        # keep the circuit on the generic kernel family (QNN_CREATE_GENERIC_ONLY): the parity tests use it to
+        # check one kernel family against the other
+        self.generic_only = bool(generic_only)
         self.ops: Tuple[Op, ...] = tuple(ops)
         for op in self.ops:
             if op.kind not in _lib.GATE:
@@ -65,6 +68,15 @@ class Circuit:
                     raise ValueError(f"angle source must be 'w', 'x' or 'c', got {what!r}")
         return arr
 
+    def _create(self, out):
+        flags = _lib.CREATE_GENERIC_ONLY if self.generic_only else 0
+        return _lib.lib().qnn_circuit_create_ex(self.c_ops(), len(self.ops), self.n_qubits, self.n_inputs,
+                                                self.n_weights, _lib.ENCODER[self.encoder], flags, C.byref(out))
+
+    def generic(self) -> "Circuit":
+        """The same gate list, pinned to the generic kernel family."""
+        return Circuit(self.n_qubits, self.ops, self.n_inputs, self.n_weights, self.encoder, generic_only=True)
+
     def handle(self, device_index: int):
         """``qnn_circuit*`` for a CUDA device (created on first use, with that device current)."""
         h = self._handles.get(device_index)
@@ -72,8 +84,7 @@ class Circuit:
             import torch
             out = C.c_void_p()
             with torch.cuda.device(device_index):
-                rc = _lib.lib().qnn_circuit_create(self.c_ops(), len(self.ops), self.n_qubits, self.n_inputs,
-                                                   self.n_weights, _lib.ENCODER[self.encoder], C.byref(out))
+                rc = self._create(out)
             _lib.check(rc, "qnn_circuit_create")
             h = out
             self._handles[device_index] = h
@@ -88,9 +99,7 @@ class Circuit:
             h, own = next(iter(self._handles.values())), False
         else:
             h, own = C.c_void_p(), True
-            _lib.check(lib.qnn_circuit_create(self.c_ops(), len(self.ops), self.n_qubits, self.n_inputs,
-                                              self.n_weights, _lib.ENCODER[self.encoder], C.byref(h)),
-                       "qnn_circuit_create")
+            _lib.check(self._create(h), "qnn_circuit_create")
         try:
             need = lib.qnn_circuit_describe(h, None, 0)
             buf = C.create_string_buffer(need)
@@ -113,10 +122,11 @@ class Circuit:
 
     def __getstate__(self):
         return {"n_qubits": self.n_qubits, "n_inputs": self.n_inputs, "n_weights": self.n_weights,
-                "encoder": self.encoder, "ops": self.ops}
+                "encoder": self.encoder, "ops": self.ops, "generic_only": self.generic_only}
 
     def __setstate__(self, st):
-        self.__init__(st["n_qubits"], st["ops"], st["n_inputs"], st["n_weights"], st["encoder"])
+        self.__init__(st["n_qubits"], st["ops"], st["n_inputs"], st["n_weights"], st["encoder"],
+                      st.get("generic_only", False))
 
     def __repr__(self):
         return (f"Circuit(n_qubits={self.n_qubits}, n_ops={len(self.ops)}, n_inputs={self.n_inputs}, "

@@ -23,7 +23,7 @@ namespace {
 
 constexpr int kHeadMaxN = 16;           // n_qubits <= 16 everywhere in this library
 constexpr int kHeadMaxK = 4096;         // feature columns
-constexpr int kHeadBwdGrid = 148 * 2;   // persistent backward grid: partial sums per CTA
+constexpr int kHeadBwdCtasPerSm = 2;    // persistent backward grid (two CTAs per SM): partial sums per CTA
 constexpr int kChunk = 32;              // samples per backward chunk
 
 __global__ void __launch_bounds__(256) k_head_fwd(const float* __restrict__ f, const float* __restrict__ W,
@@ -124,7 +124,7 @@ int check_shape(const char* fn, int64_t B, int K, int n) {
   return QNN_OK;
 }
 
-int bwd_grid(int64_t B) { return (int)std::max<int64_t>(1, std::min<int64_t>((B + kChunk - 1) / kChunk, kHeadBwdGrid)); }
+int bwd_grid(int64_t B) { return (int)std::max<int64_t>(1, std::min<int64_t>((B + kChunk - 1) / kChunk, (int64_t)qnn_sm_count() * kHeadBwdCtasPerSm)); }
 
 }  // namespace
 
@@ -138,8 +138,8 @@ extern "C" int qnn_head_forward(const float* f, const float* W, const float* bia
   if (int rc = check_shape("qnn_head_forward", B, K, n)) return rc;
   if (!f || !W || !bias || !x) { qnn_set_error("qnn_head_forward: NULL buffer"); return QNN_ERR_INVALID; }
   const size_t smem = (size_t)n * K * sizeof(float);
-  if (smem > 48 * 1024) QNN_CUDA_CHECK(cudaFuncSetAttribute(k_head_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((B + 7) / 8, 148 * 4));
+  if (int rc = qnn_allow_smem(reinterpret_cast<const void*>(k_head_fwd), smem)) return rc;
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((B + 7) / 8, (int64_t)qnn_sm_count() * 4));
   k_head_fwd<<<grid, 256, smem, static_cast<cudaStream_t>(cuda_stream)>>>(f, W, bias, x, B, K, n);
   QNN_CUDA_CHECK(cudaGetLastError());
   return QNN_OK;

@@ -53,7 +53,7 @@ extern "C" int qnn_pruned_adamw_step_counted(float* params, float* grads, float*
   if (!params || !grads || !exp_avg || !exp_avg_sq || !steps_done) { qnn_set_error("qnn_pruned_adamw_step_counted: NULL buffer"); return QNN_ERR_INVALID; }
   if (n <= 0) { qnn_set_error("qnn_pruned_adamw_step_counted: n=%lld must be positive", (long long)n); return QNN_ERR_INVALID; }
   cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
-  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, 148 * 8));
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, (int64_t)qnn_sm_count() * 8));
   k_pruned_adamw<<<grid, 256, 0, st>>>(params, grads, exp_avg, exp_avg_sq, n, lr, beta1, beta2, eps, weight_decay, 0.f, 1.f,
                                        prune_threshold, pruned_count, steps_done);
   QNN_CUDA_CHECK(cudaGetLastError());
@@ -69,7 +69,7 @@ extern "C" int qnn_pruned_adamw_step(float* params, float* grads, float* exp_avg
   if (n <= 0 || step < 1) { qnn_set_error("qnn_pruned_adamw_step: n=%lld, step=%lld must be positive", (long long)n, (long long)step); return QNN_ERR_INVALID; }
   const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
   const float step_size = (float)((double)lr / bc1), bc2_sqrt = (float)sqrt(bc2);
-  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, 148 * 8));
+  const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, (int64_t)qnn_sm_count() * 8));
   k_pruned_adamw<<<grid, 256, 0, static_cast<cudaStream_t>(cuda_stream)>>>(params, grads, exp_avg, exp_avg_sq, n, lr, beta1,
                                                                            beta2, eps, weight_decay, step_size, bc2_sqrt,
                                                                            prune_threshold, pruned_count, nullptr);

@@ -12,7 +12,7 @@
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kMaxCtas = 148 * 4;
+constexpr int kMaxCtasPerSm = 4;
 
 struct Stats {
   float mean, rstd;
@@ -82,6 +82,7 @@ __global__ void __launch_bounds__(kThreads) k_apply(const float* __restrict__ y,
                                                     float* __restrict__ yn_out, float* __restrict__ stats, long long total,
                                                     int n, qnat_params p) {
   __shared__ float smean[QNN_MAX_QUBITS], srstd[QNN_MAX_QUBITS];
+  if (Bt <= 0 && p.normalise) Bt = llrint(sums[2 * n]);   // row count kept (and all-reduced) next to the sums
   if (threadIdx.x < n) {
     Stats s = {0.f, 1.f};
     if (p.normalise) s = stats_from_sums(sums, threadIdx.x, n, Bt, p.eps);
@@ -108,6 +109,7 @@ __global__ void __launch_bounds__(kThreads) k_bwd_apply(const float* __restrict_
                                                         const double* __restrict__ bsums, long long Bt, float* __restrict__ gy,
                                                         long long total, int n, qnat_params p) {
   __shared__ float smean[QNN_MAX_QUBITS], srstd[QNN_MAX_QUBITS], sa[QNN_MAX_QUBITS], sb[QNN_MAX_QUBITS];
+  if (Bt <= 0 && p.normalise) Bt = llrint(bsums[2 * n]);
   if (threadIdx.x < n && p.normalise) {
     smean[threadIdx.x] = stats[threadIdx.x];
     srstd[threadIdx.x] = stats[n + threadIdx.x];
@@ -130,7 +132,7 @@ __global__ void __launch_bounds__(kThreads) k_bwd_apply(const float* __restrict_
 int n_ctas_for(long long B, int n) {
   const int rows_per_pass = kThreads / n;
   long long c = (B + rows_per_pass - 1) / rows_per_pass;
-  return (int)std::max<long long>(1, std::min<long long>(c, kMaxCtas));
+  return (int)std::max<long long>(1, std::min<long long>(c, (long long)qnn_sm_count() * kMaxCtasPerSm));
 }
 
 int check(const char* fn, int64_t B, int32_t n, const qnat_params* p) {
@@ -167,8 +169,9 @@ extern "C" int qnat_apply(const float* y, const float* noise, const double* sums
   int rc = check("qnat_apply", B, n, p);
   if (rc) return rc;
   if (!y || !out || !p || (p->normalise && !sums)) { qnn_set_error("qnat_apply: NULL pointer"); return QNN_ERR_INVALID; }
+  if (B_total < 0) { qnn_set_error("qnat_apply: B_total=%lld is negative", (long long)B_total); return QNN_ERR_INVALID; }
   const long long total = (long long)B * n;
-  const int g = (int)std::max<long long>(1, std::min<long long>((total + kThreads - 1) / kThreads, 148 * 8));
+  const int g = (int)std::max<long long>(1, std::min<long long>((total + kThreads - 1) / kThreads, (long long)qnn_sm_count() * 8));
   k_apply<<<g, kThreads, 0, static_cast<cudaStream_t>(cuda_stream)>>>(y, p->sigma != 0.f ? noise : nullptr, sums, B_total, out, yn, stats, total, n, *p);
   QNN_CUDA_CHECK(cudaGetLastError());
   return QNN_OK;
@@ -197,7 +200,7 @@ extern "C" int qnat_backward_apply(const float* gout, const float* y, const floa
   if (rc) return rc;
   if (!gout || !gy || !p || (p->quantise && !yn) || (p->normalise && (!stats || !bsums || !y))) { qnn_set_error("qnat_backward_apply: NULL pointer"); return QNN_ERR_INVALID; }
   const long long total = (long long)B * n;
-  const int g = (int)std::max<long long>(1, std::min<long long>((total + kThreads - 1) / kThreads, 148 * 8));
+  const int g = (int)std::max<long long>(1, std::min<long long>((total + kThreads - 1) / kThreads, (long long)qnn_sm_count() * 8));
   k_bwd_apply<<<g, kThreads, 0, static_cast<cudaStream_t>(cuda_stream)>>>(gout, y, yn, stats, bsums, B_total, gy, total, n, *p);
   QNN_CUDA_CHECK(cudaGetLastError());
   return QNN_OK;

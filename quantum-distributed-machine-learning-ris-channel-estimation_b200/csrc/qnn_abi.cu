@@ -4,6 +4,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
+#include <map>
+#include <mutex>
 #include <new>
 
 #include "qnn_internal.h"
@@ -21,6 +24,31 @@ void qnn_set_error(const char* fmt, ...) {
 extern "C" const char* qnn_last_error(void) { return g_err; }
 extern "C" int32_t qnn_abi_version(void) { return QNN_ABI_VERSION; }
 
+int qnn_sm_count() {
+  static std::atomic<int> cache[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) { (void)cudaGetLastError(); return 148; }
+  if (dev >= 0 && dev < 64) { const int v = cache[dev].load(std::memory_order_relaxed); if (v > 0) return v; }
+  int sms = 0;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) { (void)cudaGetLastError(); return 148; }
+  if (dev >= 0 && dev < 64) cache[dev].store(sms, std::memory_order_relaxed);
+  return sms;
+}
+
+int qnn_allow_smem(const void* kernel, size_t smem) {
+  if (smem <= 48 * 1024) return QNN_OK;
+  static std::mutex mu;
+  static std::map<std::pair<const void*, int>, size_t> allowed;
+  int dev = 0;
+  QNN_CUDA_CHECK(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(mu);
+  size_t& have = allowed[{kernel, dev}];
+  if (have >= smem) return QNN_OK;
+  QNN_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  have = smem;
+  return QNN_OK;
+}
+
 static int n_angles(int kind) {
   switch (kind) {
     case QNN_RX: case QNN_RY: case QNN_RZ: return 1;
@@ -33,8 +61,14 @@ static bool two_qubit(int kind) { return kind == QNN_CNOT || kind == QNN_CZ || k
 
 extern "C" int qnn_circuit_create(const qnn_op* ops, int32_t n_ops, int32_t n_qubits, int32_t n_inputs,
                                   int32_t n_weights, int32_t encoder, qnn_circuit** out) {
+  return qnn_circuit_create_ex(ops, n_ops, n_qubits, n_inputs, n_weights, encoder, 0u, out);
+}
+
+extern "C" int qnn_circuit_create_ex(const qnn_op* ops, int32_t n_ops, int32_t n_qubits, int32_t n_inputs,
+                                     int32_t n_weights, int32_t encoder, uint32_t flags, qnn_circuit** out) {
   if (!out) { qnn_set_error("qnn_circuit_create: out is NULL"); return QNN_ERR_INVALID; }
   *out = nullptr;
+  if (flags & ~(uint32_t)QNN_CREATE_GENERIC_ONLY) { qnn_set_error("qnn_circuit_create_ex: unknown flags 0x%x", flags); return QNN_ERR_INVALID; }
   if (n_qubits < 1 || n_qubits > QNN_MAX_QUBITS) {
     qnn_set_error("n_qubits=%d outside [1, %d]", n_qubits, QNN_MAX_QUBITS);
     return QNN_ERR_INVALID;
@@ -120,6 +154,7 @@ extern "C" int qnn_circuit_create(const qnn_op* ops, int32_t n_ops, int32_t n_qu
     *out = c;
     return QNN_OK;
   }
+  c->num_sm = qnn_sm_count();
   auto upload = [&](void** dptr, const void* src, size_t bytes) -> cudaError_t {
     cudaError_t err = cudaMalloc(dptr, bytes ? bytes : 16);
     if (err != cudaSuccess) return err;
@@ -135,8 +170,7 @@ extern "C" int qnn_circuit_create(const qnn_op* ops, int32_t n_ops, int32_t n_qu
   if (c->vm && c->vm->ok) {
     int rc = vm::upload(c->vm, n_weights);
     if (rc != QNN_OK) { qnn_circuit_destroy(c); return rc; }
-    const char* off = getenv("QNN_DISABLE_VM");
-    c->use_vm = !(off && off[0] == '1');
+    c->use_vm = !(flags & QNN_CREATE_GENERIC_ONLY);
   }
   *out = c;
   return QNN_OK;
@@ -175,11 +209,10 @@ static bool vm_plan(const qnn_circuit* c, int64_t B, vm::Plan* pl) {
 extern "C" const char* qnn_circuit_plan(const qnn_circuit* c, int64_t B) {
   if (!c) return "";
   vm::Plan vp;
-  if (vm_plan(c, B, &vp)) { c->plan_name = "vm-register"; return c->plan_name.c_str(); }
+  if (vm_plan(c, B, &vp)) return "vm-register";
   GenericPlan p;
   generic_plan(c, B, &p);
-  c->plan_name = p.name;
-  return c->plan_name.c_str();
+  return p.name;   // a string literal
 }
 
 extern "C" int32_t qnn_forward_launches(const qnn_circuit* c, int64_t B) {
@@ -212,10 +245,16 @@ extern "C" size_t qnn_backward_workspace_bytes(const qnn_circuit* c, int64_t B) 
   return p.ws_coef + p.ws_state_bwd + p.ws_partial;
 }
 
-static int check_common(const char* fn, const qnn_circuit* c, const float* x, const float* w, int64_t B) {
+int qnn_check_common(const char* fn, const qnn_circuit* c, const float* x, const float* w, int64_t B) {
   if (!c) { qnn_set_error("%s: circuit is NULL", fn); return QNN_ERR_INVALID; }
   if (B <= 0) { qnn_set_error("%s: B=%lld must be positive", fn, (long long)B); return QNN_ERR_INVALID; }
   if (c->device < 0) { qnn_set_error("%s: the circuit was created without a CUDA device; there is no CPU path", fn); return QNN_ERR_CUDA; }
+  int dev = -1;
+  QNN_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev != c->device) {   // the lowered program and its tables live on the creating device
+    qnn_set_error("%s: the circuit was created on device %d but device %d is current", fn, c->device, dev);
+    return QNN_ERR_INVALID;
+  }
   if (!x && c->n_inputs > 0) { qnn_set_error("%s: x is NULL", fn); return QNN_ERR_INVALID; }
   if (!w && c->n_weights > 0) { qnn_set_error("%s: w is NULL", fn); return QNN_ERR_INVALID; }
   return QNN_OK;
@@ -229,7 +268,7 @@ extern "C" size_t qnn_state_bytes(const qnn_circuit* c, int64_t B) {
 
 static int forward_impl(const char* fn, const qnn_circuit* c, const float* x, const float* w, float* y, float* state,
                         int64_t B, void* workspace, size_t workspace_bytes, void* cuda_stream) {
-  int rc = check_common(fn, c, x, w, B);
+  int rc = qnn_check_common(fn, c, x, w, B);
   if (rc) return rc;
   if (!y) { qnn_set_error("%s: y is NULL", fn); return QNN_ERR_INVALID; }
   const size_t need = qnn_forward_workspace_bytes(c, B);
@@ -248,7 +287,7 @@ static int forward_impl(const char* fn, const qnn_circuit* c, const float* x, co
 static int backward_impl(const char* fn, const qnn_circuit* c, const float* x, const float* w, const float* gy,
                          const float* state, float* gx, float* gw, int64_t B, void* workspace, size_t workspace_bytes,
                          void* cuda_stream) {
-  int rc = check_common(fn, c, x, w, B);
+  int rc = qnn_check_common(fn, c, x, w, B);
   if (rc) return rc;
   if (!gy) { qnn_set_error("%s: gy is NULL", fn); return QNN_ERR_INVALID; }
   if (!gw && c->n_weights > 0) { qnn_set_error("%s: gw is NULL", fn); return QNN_ERR_INVALID; }

@@ -113,7 +113,7 @@ __device__ __forceinline__ void init_state(const Group<WARP>& g, float2* psi, in
     }
     g.template reduce<1>(s);
     const float nrm = sqrtf(s[0]);
-    const float inv = 1.f / nrm;
+    const float inv = nrm > 0.f ? 1.f / nrm : 0.f;   // an all-zero row stays the zero state (y = 0, zero gradients)
     for (unsigned k = g.tid; k < dim; k += g.size)
       psi[k] = make_float2(k < kk ? xrow[k] * inv : 0.f, 0.f);
     *nrm_out = nrm;
@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(WARP ? 256 : 1024) k_generic(KArgs a) {
       float* gxrow = a.gx + (size_t)b * a.n_inputs;
       if (a.encoder == QNN_ENC_AMPLITUDE) {
         const unsigned kk = min(dim, (unsigned)a.n_inputs);
-        const float inv = 1.f / nrm;
+        const float inv = nrm > 0.f ? 1.f / nrm : 0.f;
         float d[1] = {0.f};
         for (unsigned k = g.tid; k < kk; k += g.size) d[0] = fmaf(xrow[k] * inv, 2.f * lam[k].x, d[0]);
         g.template reduce<1>(d);
@@ -388,7 +388,7 @@ SubPlan sub_plan(const qnn_circuit* c, int64_t B, bool backward) {
   SubPlan s{};
   const int n = c->n_qubits;
   const size_t dim = (size_t)1 << n;
-  const int num_sm = 148;
+  const int num_sm = c->num_sm;
   if (n <= 10 && smem_needed(c, true, false, backward, 1) <= kSmemBudget) {
     s.mode = 0;
     int gpc = 8;
@@ -425,8 +425,7 @@ size_t align256(size_t v) { return (v + 255) & ~size_t(255); }
 template <bool BACKWARD>
 int launch(const SubPlan& s, const KArgs& a, cudaStream_t st) {
   auto go = [&](auto kern) -> int {
-    if (s.smem > 48 * 1024)
-      QNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)s.smem));
+    if (int rc = qnn_allow_smem(reinterpret_cast<const void*>(kern), s.smem)) return rc;
     kern<<<s.grid, s.threads, s.smem, st>>>(a);
     QNN_CUDA_CHECK(cudaGetLastError());
     return QNN_OK;
@@ -546,10 +545,9 @@ extern "C" size_t qnn_static_scratch_bytes(void) { return QNN_STATIC_SCRATCH_BYT
 
 extern "C" int qnn_backward_static(const qnn_circuit* c, const float* x, const float* w, const float* gy,
                                    float* gx, float* gw, int64_t B, void* cuda_stream) {
-  if (!c) { qnn_set_error("qnn_backward_static: circuit is NULL"); return QNN_ERR_INVALID; }
-  if (B <= 0) { qnn_set_error("qnn_backward_static: B=%lld must be positive", (long long)B); return QNN_ERR_INVALID; }
-  if ((!x && c->n_inputs > 0) || (!w && c->n_weights > 0) || !gy || (!gw && c->n_weights > 0)) {
-    qnn_set_error("qnn_backward_static: NULL x, w, gy or gw");
+  if (int rc = qnn_check_common("qnn_backward_static", c, x, w, B)) return rc;
+  if (!gy || (!gw && c->n_weights > 0)) {
+    qnn_set_error("qnn_backward_static: NULL gy or gw");
     return QNN_ERR_INVALID;
   }
   GenericPlan p;

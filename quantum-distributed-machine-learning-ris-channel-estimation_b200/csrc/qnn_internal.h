@@ -37,10 +37,18 @@ struct qnn_circuit {
   DevOp* d_ops = nullptr;
   int32_t* d_slot_ptr = nullptr;  // CSR weight -> slots
   int32_t* d_slot_idx = nullptr;
-  mutable std::string plan_name;
+  int num_sm = 148;               // SM count of `device` (cudaDevAttrMultiProcessorCount), read at creation
   vm::Program* vm = nullptr;      // register-resident program (qnn_vm.h); vm->ok says whether it applies
-  bool use_vm = false;            // vm->ok and not disabled by QNN_DISABLE_VM=1 (tests of the generic family)
+  bool use_vm = false;            // vm->ok and the circuit was not created with QNN_CREATE_GENERIC_ONLY
 };
+
+// SM count of the current device, cached per device ordinal (148 when it cannot be read).
+int qnn_sm_count();
+// Opt a kernel in to `smem` bytes of dynamic shared memory (cudaFuncAttributeMaxDynamicSharedMemorySize):
+// issued once per (kernel, device) and again only if a later launch needs more, not on every launch.
+int qnn_allow_smem(const void* kernel, size_t smem);
+// Argument checks shared by every compute entry point (NULL circuit / pointers, B, device the circuit lives on).
+int qnn_check_common(const char* fn, const qnn_circuit* c, const float* x, const float* w, int64_t B);
 
 void qnn_set_error(const char* fmt, ...);
 #define QNN_CUDA_CHECK(expr)                                                            \

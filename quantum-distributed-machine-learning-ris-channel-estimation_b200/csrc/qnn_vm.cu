@@ -192,7 +192,7 @@ bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
     out->smem_fwd = smem_bytes(p, n_ang_in, bwd_warps, false, true);
     out->smem_bwd = smem_bytes(p, n_ang_in, bwd_warps, true, true);
     if (out->smem_fwd > kSmemMax || out->smem_bwd > kSmemMax) return false;
-    out->n_clusters = (int)std::max<int64_t>(1, std::min<int64_t>(B, max_active_clusters_g2(out->cluster, out->smem_bwd)));
+    out->n_clusters = (int)std::max<int64_t>(1, std::min<int64_t>(B, max_active_clusters_g2(out->cluster, out->smem_bwd, c->device, c->num_sm)));
     out->grid = out->n_clusters * out->cluster;
     out->ws_cluster = align256(((size_t)out->n_clusters << (p.n + 5)) + (size_t)out->n_clusters * (1 << p.wb) * 48 * sizeof(float));
   } else {
@@ -208,7 +208,7 @@ bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
     out->smem_bwd = sb;
     const int64_t groups_per_cta = bwd_warps >> p.wb;
     const int64_t ctas = (n_batches(p, B) + groups_per_cta - 1) / groups_per_cta;
-    out->grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, 148));   // backward: one CTA per SM
+    out->grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, c->num_sm));   // backward: one CTA per SM
   }
   out->ws_coef = align256(std::max<size_t>(p.coef_ops.size(), 1) * QNN_COEF_STRIDE * sizeof(float));
   out->ws_diag = align256(((size_t)p.n_big_tables * (1024u << p.wb) + (size_t)p.n_small_tables * 32 + 1) * sizeof(float2));
@@ -268,7 +268,7 @@ int forward(const qnn_circuit* c, const Program& p, const Plan& pl, const float*
   if (pl.cluster == 0) {
     const int64_t groups_per_cta = (pl.fwd_threads / 32) >> p.wb;
     const int64_t ctas = (n_batches(p, B) + groups_per_cta - 1) / groups_per_cta;
-    grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, 148));
+    grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, c->num_sm));
   }
   const LaunchCfg lc{grid, pl.fwd_threads, pl.cluster, pl.smem_fwd, st};
   const bool state_on = a.state != nullptr;

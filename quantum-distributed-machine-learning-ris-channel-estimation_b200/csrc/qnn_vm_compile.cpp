@@ -170,7 +170,7 @@ struct Builder {
   // (a trailing diagonal: no effect on <Z>); keep it inside the gate body when a controlled gate or a CNOT
   // would otherwise force a diagonal of its own.
   void defer_phases() {
-    static const bool no_defer = [] { const char* e = getenv("QNN_VM_NO_DEFER"); return e && e[0] == '1'; }();   // A/B knob
+    const bool no_defer = false;
     std::vector<Item> out;
     for (size_t i = 0; i < items.size(); ++i) {
       if (items[i].kind == IT_CP) continue;                   // placeholders are re-emitted below

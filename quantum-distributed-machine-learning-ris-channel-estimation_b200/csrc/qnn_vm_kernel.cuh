@@ -91,7 +91,7 @@ __device__ __forceinline__ float2 swp(float2 a) { return make_float2(a.y, a.x); 
 // Real rotation [[c,-s],[s,c]] (c,s = cos,sin(phi)) as three in-place shears
 //   a0 += al*a1;  a1 += be*a0;  a0 += al*a1       al = -tan(phi/2), be = sin(phi)
 // 3 packed FMAs per amplitude pair, no temporaries; the inverse uses (-al, -be).  phi is range-reduced to
-// [-pi/2, pi/2] when the coefficients are made, so |al| <= 0.415.
+// [-pi/2, pi/2] when the coefficients are made, so |al| = |tan(phi/2)| <= 1.
 template <int RB>
 __device__ __forceinline__ void rot(float2 (&st)[NA], float al, float be) {
 #pragma unroll
@@ -555,7 +555,10 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
         ps[j].x = v;
         ss = fmaf(v, v, ss);
       }
-      const float inv = rsqrtf(sample_sum(ss, lbits));
+      // padding samples of a ragged last batch (and all-zero rows) carry the zero state: rsqrt(0) would put NaNs
+      // into the warp-wide weight-gradient sums
+      const float ssum = sample_sum(ss, lbits);
+      const float inv = (active && ssum > 0.f) ? rsqrtf(ssum) : 0.f;
 #pragma unroll
       for (int j = 0; j < NA; ++j) ps[j].x *= inv;
     } else {
@@ -843,7 +846,8 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
             ss = fmaf(xv[j], xv[j], ss);
             dot = fmaf(xv[j], 2.f * ls[j].x, dot);
           }
-          const float inv = rsqrtf(sample_sum(ss, lbits));
+          const float ssum = sample_sum(ss, lbits);
+          const float inv = (active && ssum > 0.f) ? rsqrtf(ssum) : 0.f;
           dot = sample_sum(dot, lbits) * inv;
 #pragma unroll
           for (int j = 0; j < NA; ++j) {
@@ -890,7 +894,7 @@ struct LaunchCfg { int grid, threads, cluster; size_t smem; cudaStream_t stream;
 
 template <typename K>
 int launch_kernel(K kern, const LaunchCfg& lc, const VmArgs& a) {
-  if (lc.smem > 48 * 1024) QNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lc.smem));
+  if (int rc = qnn_allow_smem(reinterpret_cast<const void*>(kern), lc.smem)) return rc;
   if (lc.cluster == 0) {
     kern<<<lc.grid, lc.threads, lc.smem, lc.stream>>>(a);
   } else {
@@ -917,6 +921,6 @@ int launch_g0(bool bwd, bool state, const LaunchCfg& lc, const VmArgs& a);    //
 int launch_g0a(bool bwd, bool state, const LaunchCfg& lc, const VmArgs& a);   // n <= 10, amplitude encoder
 int launch_g1(bool bwd, bool state, const LaunchCfg& lc, const VmArgs& a);    // n = 11..13
 int launch_g2(bool bwd, bool state, const LaunchCfg& lc, const VmArgs& a);    // n = 14..16 (clusters)
-int max_active_clusters_g2(int cluster, size_t smem);
+int max_active_clusters_g2(int cluster, size_t smem, int device, int num_sm);
 
 }  // namespace vm

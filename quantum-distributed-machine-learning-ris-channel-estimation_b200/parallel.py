@@ -33,7 +33,9 @@ class FlatGradBucket:
         if not self.params:
             raise ValueError("no trainable parameters")
         dev, total = self.params[0].device, sum(p.numel() for p in self.params)
-        self.flat = torch.zeros(total, dtype=torch.float32, device=dev)
+        # one spare element behind the gradients carries this rank's row count through the same all-reduce
+        self._buf = torch.zeros(total + 1, dtype=torch.float32, device=dev)
+        self.flat = self._buf[:total]
         off = 0
         self.slices = []
         for p in self.params:
@@ -50,13 +52,25 @@ class FlatGradBucket:
             if p.grad is None or p.grad.data_ptr() != self.flat[a:b].data_ptr():
                 p.grad = self.flat[a:b].view_as(p)
 
-    def all_reduce(self, group: Optional[dist.ProcessGroup] = None, average: bool = True) -> None:
+    def all_reduce(self, group: Optional[dist.ProcessGroup] = None, average: bool = True,
+                   local_rows: Optional[int] = None) -> None:
         """Sum over ranks (then / world if ``average``): with equal shard sizes and per-shard mean
-        losses this reproduces the single-process gradient of the global-batch mean loss."""
+        losses this reproduces the single-process gradient of the global-batch mean loss.
+
+        ``local_rows``: this rank's number of samples when shards are NOT equal (ragged tail of
+        ``shard_range``, last batch of an epoch).  Each rank's mean-loss gradient is then weighted by its
+        row count and the sum divided by the global count, which travels in the same collective (no host
+        round trip): the result is the gradient of the mean over the global batch whatever the split."""
         if not (dist.is_available() and dist.is_initialized()):
             return
         world = dist.get_world_size(group)
         if world == 1:
+            return
+        if local_rows is not None and average:
+            self.flat.mul_(float(local_rows))
+            self._buf[-1] = float(local_rows)
+            dist.all_reduce(self._buf, op=dist.ReduceOp.SUM, group=group)
+            self.flat.div_(self._buf[-1])
             return
         dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
         if average:

@@ -36,7 +36,10 @@ class _QnatFunction(torch.autograd.Function):
         out = torch.empty_like(yc)
         yn = torch.empty_like(yc)
         stats = torch.empty(2 * n, dtype=torch.float32, device=yc.device)
-        sums = torch.zeros(2 * n, dtype=torch.float64, device=yc.device)
+        # [sum y (n), sum y^2 (n), row count]: the count rides along with the sums through the all-reduce, so
+        # ranks with unequal shard sizes (ragged tail of parallel.shard_range, last batch of an epoch) all
+        # normalise with the true global count -- read on the device (B_total = 0), no host round trip
+        sums = torch.zeros(2 * n + 1, dtype=torch.float64, device=yc.device)
         B_total = B
         nz = None if noise is None else noise.detach().to(torch.float32).contiguous()
         with torch.cuda.device(dev):
@@ -46,11 +49,12 @@ class _QnatFunction(torch.autograd.Function):
                 _lib.check(lib.qnat_batch_sums(_ptr(yc), _ptr(sums), B, n, _ptr(ws), ws.numel(), st), "qnat_batch_sums")
                 if group is not None:
                     import torch.distributed as dist
+                    sums[2 * n] = float(B)
                     dist.all_reduce(sums, group=group)
-                    B_total = B * dist.get_world_size(group)
+                    B_total = 0
             _lib.check(lib.qnat_apply(_ptr(yc), _ptr(nz), _ptr(sums), B_total, _ptr(out), _ptr(yn), _ptr(stats),
                                       B, n, C.byref(p), st), "qnat_apply")
-        ctx.save_for_backward(yc, yn, stats)
+        ctx.save_for_backward(yc, yn, stats, sums)
         ctx.p, ctx.group, ctx.B_total = p, group, B_total
         return out
 
@@ -58,11 +62,11 @@ class _QnatFunction(torch.autograd.Function):
     @once_differentiable
     def backward(ctx, gout):
         lib = _lib.lib()
-        yc, yn, stats = ctx.saved_tensors
+        yc, yn, stats, sums = ctx.saved_tensors
         B, n = yc.shape
         g = gout.detach().to(torch.float32).contiguous()
         gy = torch.empty_like(yc)
-        bsums = torch.zeros(2 * n, dtype=torch.float64, device=yc.device)
+        bsums = torch.zeros(2 * n + 1, dtype=torch.float64, device=yc.device)
         dev = yc.device.index
         p = ctx.p
         with torch.cuda.device(dev):
@@ -74,6 +78,7 @@ class _QnatFunction(torch.autograd.Function):
                 if ctx.group is not None:
                     import torch.distributed as dist
                     dist.all_reduce(bsums, group=ctx.group)
+                    bsums[2 * n] = sums[2 * n]          # the global row count of the forward pass
             _lib.check(lib.qnat_backward_apply(_ptr(g), _ptr(yc), _ptr(yn), _ptr(stats), _ptr(bsums), ctx.B_total,
                                                _ptr(gy), B, n, C.byref(p), st), "qnat_backward_apply")
         return gy, None, None, None

@@ -25,6 +25,7 @@ CASES = {
     "u3cu3_n10_L3": ("u3", 10, 3, "none", 4),     # BASELINE config 3 circuit
     "u3cu3_amp_n4_L2": ("u3amp", 4, 2, "amplitude", 8),
     "u3cu3_n12_L2": ("u3", 12, 2, "none", 2),
+    "u3cu3_n16_L8": ("u3", 16, 8, "none", 2),     # BASELINE config 4's exact circuit (768 weights, 512 KiB per state)
 }
 
 

@@ -28,8 +28,9 @@ def assert_close(actual, expected, rel=REL_TOL, scale=1.0, what=""):
     a = np.asarray(actual, dtype=np.float64)
     b = np.asarray(expected, dtype=np.float64)
     assert a.shape == b.shape, f"{what}: shape {a.shape} vs {b.shape}"
+    assert np.isfinite(a).all(), f"{what}: {np.count_nonzero(~np.isfinite(a))} of {a.size} elements are NaN or Inf"
     tol = rel * np.maximum(np.maximum(1.0, np.abs(b)), scale)
     err = np.abs(a - b)
-    bad = err > tol
-    assert not bad.any(), (f"{what}: {bad.sum()} of {bad.size} elements off; worst |err|={err.max():.3e} "
-                           f"(tol {tol.flat[err.argmax()]:.3e}) at {np.unravel_index(err.argmax(), err.shape)}")
+    bad = ~(err <= tol)          # NaN compares false either way: count it as off, never as close
+    assert not bad.any(), (f"{what}: {bad.sum()} of {bad.size} elements off; worst |err|={np.nanmax(err):.3e} "
+                           f"(tol {tol.flat[np.nanargmax(err)]:.3e}) at {np.unravel_index(np.nanargmax(err), err.shape)}")

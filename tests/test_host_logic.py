@@ -10,7 +10,9 @@ import qris_b200
 from qris_b200 import estimators as E
 from qris_b200 import pennylane_shim as qml
 
-REF = "/root/reference/Estimators_QuantumNAT_onchipQNN.py"
+from oracle import stage_reference
+
+REF = stage_reference.locate() or stage_reference.SOURCE
 
 
 def test_reference_circuit_gate_order():
@@ -95,7 +97,15 @@ def test_product_never_imports_the_oracle():
                 assert "import oracle" not in src and "from oracle" not in src, f
 
 
-@pytest.mark.skipif(not os.path.exists(REF), reason="reference checkout not present (GPU box)")
+@pytest.mark.skipif(not os.path.exists(stage_reference.SOURCE), reason="reference checkout not present")
+def test_staged_reference_file_is_the_reference_byte_for_byte():
+    """oracle/_ref/ carries the reference's estimator file to the GPU box; it must be the unmodified file."""
+    assert stage_reference.stage()
+    assert open(stage_reference.STAGED, "rb").read() == open(stage_reference.SOURCE, "rb").read()
+    assert open(stage_reference.STAGED + ".sha256").read().strip() == stage_reference.sha256(stage_reference.SOURCE)
+
+
+@pytest.mark.skipif(not os.path.exists(REF), reason="reference file neither checked out nor staged")
 def test_unmodified_reference_module_builds_on_the_shim():
     """With the shim installed as `pennylane`, the reference's own Estimators file constructs QSC_P128
     and the traced gate list equals ours.  (Structure only: nothing is executed on the CPU.)"""

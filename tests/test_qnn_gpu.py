@@ -78,6 +78,45 @@ def test_largest_sizes(n, B):
     check_against_oracle(circ, B, seed=n)
 
 
+def test_config4_exact_circuit():
+    """BASELINE configs[3] as bench.py runs it: 16 qubits, U3+CU3, EIGHT layers (768 weights), both the plain
+    pair and the saved-state pair, against the oracle and the frozen golden vector of the same circuit."""
+    circ = qris_b200.u3cu3_circuit(16, 8)
+    assert _plan(circ, 2) == "vm-register" and circ.n_weights == 768
+    check_against_oracle(circ, 2, seed=168)
+    x, w, gy = (t.cuda() for t in seeded_inputs(circ, 3, seed=169))
+    y1, state = qris_b200.qnn_forward_raw(circ, x, w, save_state=True)
+    gx0, gw0 = qris_b200.qnn_backward_raw(circ, x, w, gy)
+    gx1, gw1 = qris_b200.qnn_backward_raw(circ, x, w, gy, state=state)
+    assert torch.equal(y1, qris_b200.qnn_forward_raw(circ, x, w))
+    assert_close(gx1.cpu().numpy(), gx0.cpu().numpy(), scale=float(gx0.abs().max()), what="gx saved vs recompute")
+    assert_close(gw1.cpu().numpy(), gw0.cpu().numpy(), scale=float(gw0.abs().max()), what="gw saved vs recompute")
+
+
+@pytest.mark.parametrize("n,n_inputs,B", [(6, 50, 33), (5, 32, 40), (8, 300, 7), (9, 1, 3), (7, 128, 1), (10, 1024, 5)])
+def test_amplitude_encoder_ragged_batches_are_finite(n, n_inputs, B):
+    """A warp carries 2^(10-n) samples; the padding samples of a partly filled last warp must not leak NaNs
+    into the warp-wide weight-gradient sums (plain pair and saved-state pair), and an all-zero row is the
+    zero state: y = 0 and zero gradients, not NaN."""
+    base = qris_b200.u3cu3_circuit(n, 2, encoder="amplitude")
+    circ = qris_b200.Circuit(n, base.ops, n_inputs=n_inputs, n_weights=base.n_weights, encoder="amplitude")
+    x, w, gy = seeded_inputs(circ, B, seed=n + B)
+    xd, wd, gd = x.cuda(), w.cuda(), gy.cuda()
+    yo, gxo, gwo = O.forward_and_grads(oracle_ops(circ), n, x, w, gy, encoder="amplitude")
+    y, state = qris_b200.qnn_forward_raw(circ, xd, wd, save_state=True)
+    for st in (None, state):
+        gx, gw = qris_b200.qnn_backward_raw(circ, xd, wd, gd, state=st)
+        assert torch.isfinite(gx).all() and torch.isfinite(gw).all() and torch.isfinite(y).all()
+        assert_close(gw.cpu().numpy(), gwo.numpy(), scale=float(gwo.abs().max()), what="gw")
+        assert_close(gx.cpu().numpy(), gxo.numpy(), scale=float(gxo.abs().max()), what="gx")
+    xz = xd.clone(); xz[B // 2] = 0
+    for c in (circ, circ.generic()):
+        yz = qris_b200.qnn_forward_raw(c, xz, wd)
+        gxz, gwz = qris_b200.qnn_backward_raw(c, xz, wd, gd)
+        assert torch.isfinite(yz).all() and torch.isfinite(gxz).all() and torch.isfinite(gwz).all()
+        assert yz[B // 2].abs().max() == 0 and gxz[B // 2].abs().max() == 0
+
+
 def test_deep_cluster_circuit_falls_back_to_l2_exchanges():
     """Programs whose tables leave no room for the 64 KB local-exchange buffer are compiled with L2
     exchanges only and still run on the VM."""
@@ -91,10 +130,9 @@ def test_deep_cluster_circuit_falls_back_to_l2_exchanges():
     assert sum(x["local"] for x in c16.describe()["exchanges"]) > 0 and _plan(c16, 2) == "vm-register"
 
 
-def test_largest_sizes_generic_family(monkeypatch):
-    monkeypatch.setenv("QNN_DISABLE_VM", "1")
+def test_largest_sizes_generic_family():
     for n, B in ((14, 2), (16, 1)):
-        circ = qris_b200.u3cu3_circuit(n, 1)
+        circ = qris_b200.u3cu3_circuit(n, 1).generic()
         assert _plan(circ, B) == "generic-cta-global"
         check_against_oracle(circ, B, seed=n)
 
@@ -172,6 +210,16 @@ def test_full_size_properties(kind, n, L, B):
     assert torch.equal(gw3, gw)
     if kind == "ref":   # (5) last layer's RZ angles have identically zero gradient
         assert gw.reshape(L, n, 2)[L - 1, :, 1].abs().max().item() <= 1e-3 * scale
+    # (6) the batch reduction itself: gw of a contiguous 2,048-sample slice, taken from inside the full batch so
+    #     that several CTAs and the finalize kernel take part, against the oracle's gw of the same rows
+    lo, cnt = B // 4 + 3, min(2048, B // 2)
+    _, gws = qris_b200.qnn_backward_raw(circ, xd[lo:lo + cnt].contiguous(), wd, gd[lo:lo + cnt].contiguous(), need_gx=False)
+    _, _, gwo = O.forward_and_grads(oracle_ops(circ), n, x[lo:lo + cnt], w, gy[lo:lo + cnt])
+    assert_close(gws.cpu().numpy(), gwo.numpy(), scale=float(gwo.abs().max()), what="gw of a 2048-row slice")
+    # ... and the full-batch gw is that slice's gw plus the gw of the rest (additivity against an oracle-pinned part)
+    rest = torch.cat([torch.arange(0, lo), torch.arange(lo + cnt, B)]).to(dev)
+    _, gwr = qris_b200.qnn_backward_raw(circ, xd[rest].contiguous(), wd, gd[rest].contiguous(), need_gx=False)
+    assert_close((gws + gwr).cpu().numpy(), gw.cpu().numpy(), rel=2e-5, scale=scale, what="gw = slice + rest")
 
 
 def test_error_paths():
@@ -191,18 +239,15 @@ def test_error_paths():
     assert qris_b200.qnn_forward_raw(circ, torch.zeros(0, 4, device="cuda"), w).shape == (0, 4)
 
 
-def test_kernel_family_selection_and_both_families_agree(monkeypatch):
-    """n in [5, 10] runs on the register-resident VM; QNN_DISABLE_VM=1 (read at circuit creation) keeps
-    a circuit on the generic interpreter.  Both must match the oracle and each other."""
+def test_kernel_family_selection_and_both_families_agree():
+    """n in [5, 16] runs on the register-resident VM; a circuit created with QNN_CREATE_GENERIC_ONLY
+    (``Circuit.generic()``) stays on the generic interpreter.  Both must match the oracle and each other."""
     for make in (lambda: qris_b200.reference_circuit(6, 3), lambda: qris_b200.u3cu3_circuit(10, 2),
                  lambda: qris_b200.u3cu3_circuit(7, 2), lambda: qris_b200.reference_circuit(9, 2)):
-        monkeypatch.delenv("QNN_DISABLE_VM", raising=False)
         fast = make()
         assert _plan(fast, 64) == "vm-register"
-        monkeypatch.setenv("QNN_DISABLE_VM", "1")
-        slow = make()
+        slow = make().generic()
         assert _plan(slow, 64).startswith("generic")
-        monkeypatch.delenv("QNN_DISABLE_VM", raising=False)
         x, w, gy = seeded_inputs(fast, 77, seed=5)
         a, b = run_gpu(fast, x, w, gy), run_gpu(slow, x, w, gy)
         for u, v, name in zip(a, b, ("y", "gx", "gw")):

@@ -3,7 +3,7 @@
 A real-time channel-estimation loop, a process whose HBM belongs entirely to someone else's pool, or a
 bare C/FFI host cannot give ``qnn_backward`` a workspace.  ``qnn_backward_static`` keeps that scratch in
 a fixed array inside the library instead.  This file checks, through the C ABI, that it returns what
-``qnn_backward`` returns (same tolerance as the other parity tests) on calls in a row that share the
+``qnn_backward`` returns and what the CPU oracle computes (same tolerance as the other parity tests) on calls in a row that share the
 array, and that a request larger than the array is refused with a readable message.  It is named to be
 collected last, and depends on nothing the other tests leave behind.
 """
@@ -12,7 +12,8 @@ import pytest
 import torch
 
 import qris_b200
-from helpers import REL_TOL, assert_close, seeded_inputs
+from helpers import REL_TOL, assert_close, oracle_ops, seeded_inputs
+from oracle import qnn_oracle as O
 
 pytestmark = pytest.mark.gpu
 
@@ -34,7 +35,9 @@ def _backward_pair(circ, B, seed):
     L.check(lib.qnn_backward_static(h, x.data_ptr(), w.data_ptr(), gy.data_ptr(), gx.data_ptr(), gw.data_ptr(), B, st),
             "qnn_backward_static")
     torch.cuda.synchronize()
-    return (gx.cpu().numpy(), gw.cpu().numpy()), (gx_ref.cpu().numpy(), gw_ref.cpu().numpy())
+    # and the CPU oracle's gradients for the same inputs
+    _, gxo, gwo = O.forward_and_grads(oracle_ops(circ), circ.n_qubits, x.cpu(), w.cpu(), gy.cpu())
+    return (gx.cpu().numpy(), gw.cpu().numpy()), (gx_ref.cpu().numpy(), gw_ref.cpu().numpy()), (gxo.numpy(), gwo.numpy())
 
 
 def test_static_scratch_matches_workspace_version_on_calls_in_a_row():
@@ -43,10 +46,12 @@ def test_static_scratch_matches_workspace_version_on_calls_in_a_row():
     # different circuits and batches back to back: each later call finds the earlier call's leftovers
     for circ, B, seed in ((qris_b200.u3cu3_circuit(8, 2), 300, 1), (qris_b200.reference_circuit(6, 3), 4096, 2),
                           (qris_b200.u3cu3_circuit(8, 2), 37, 3)):
-        (gx, gw), (gx_ref, gw_ref) = _backward_pair(circ, B, seed)
+        (gx, gw), (gx_ref, gw_ref), (gx_or, gw_or) = _backward_pair(circ, B, seed)
         assert np.isfinite(gx).all() and np.isfinite(gw).all()
         assert_close(gx, gx_ref, rel=REL_TOL, scale=float(np.abs(gx_ref).max()), what="gx")
         assert_close(gw, gw_ref, rel=REL_TOL, scale=float(np.abs(gw_ref).max()), what="gw")
+        assert_close(gx, gx_or, rel=REL_TOL, scale=float(np.abs(gx_or).max()), what="gx vs oracle")
+        assert_close(gw, gw_or, rel=REL_TOL, scale=float(np.abs(gw_or).max()), what="gw vs oracle")
 
 
 def test_request_beyond_the_array_is_refused():
