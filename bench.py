@@ -13,6 +13,17 @@ One step = weight noise -> qnn_forward -> QuantumNAT forward -> QuantumNAT backw
 (adjoint VJP: gx and batch-reduced gw) [-> one NCCL all-reduce of gw when N > 1], on inputs resident in
 HBM (`value`); `e2e` is the same work driven through the nn.Module surface with pinned-host inputs
 copied in and the loss read back every step.  Prints ONE JSON line (rank 0).
+
+Besides the headline workload the line carries a ``secondary`` list of short device-timed records, each with
+its own roofline block, so that every number quoted in README/DESIGN comes out of a driver run: ``cfg4``
+(BASELINE configs[3]: 16 qubits, 8 layers), ``cfg2`` (configs[1]: n=6, batch 4096), ``cfg1`` (configs[0], the
+as-shipped training step: nine forwards of 256 + one backward + optimiser through ``runner.qsc_step``, eager and
+as a replayed CUDA graph), and for N > 1 ``cfg3_strong`` (BASELINE's batch of 65,536 split over the N GPUs).
+
+CPU legs (``cpu_baseline`` and ``--impl reference``) time ``oracle/``'s restatement of the reference's execution
+model (PennyLane's default.qubit + torch backprop: one tensor op per gate, autograd backward) with one fixed
+sample batch per workload (``CPU_BATCH``).  ``import pennylane`` is probed and the outcome reported in
+``cpu_baseline.pennylane``; it is not installed in this image, so the reference's own simulator is never timed.
 """
 from __future__ import annotations
 
@@ -41,6 +52,19 @@ WORKLOADS = {
     "cfg4": ("u3cu3", 16, 8, 576, False,
              "BASELINE configs[3]: 16-qubit U3+CU3 L=8 (a sample spans a cluster of 8 CTAs), adjoint backward, batch 576 per GPU"),
 }
+
+
+# One CPU sample batch per workload, used by BOTH CPU legs (cpu_baseline inside the default run and the
+# --impl reference arm), so the two figures of one box are the same measurement.
+CPU_BATCH = {"cfg3": 2048, "cfg2": 4096, "ref10": 2048, "cfg4": 8}
+
+
+def pennylane_probe():
+    try:
+        import pennylane  # noqa: F401
+        return f"installed ({getattr(pennylane, '__version__', '?')}) but not used: this arm times the oracle's restatement"
+    except Exception as e:
+        return f"not installed ({type(e).__name__}); the oracle's restatement of its execution model is timed"
 
 
 # ---- algorithmic work (flops of the circuit as the reference executes it) -----------
@@ -173,21 +197,22 @@ def pick_threads(kind, n, L, qnat):
     return best, best_t / 64
 
 
-def time_cpu(kind, n, L, qnat, target_s=12.0, max_B=4096, steps=3):
-    """Bounded sample: size B so that one step takes about target_s/4, then time `steps` steps."""
-    import torch
-    threads, per_sample = pick_threads(kind, n, L, qnat)
-    B = int(min(max_B, max(32, (target_s / 4) / max(per_sample, 1e-6))))
-    B = 1 << (B.bit_length() - 1)
+def time_cpu(wl, steps=3, warmup=1):
+    """Bounded sample: CPU_BATCH[wl] samples per step, `steps` timed steps after `warmup`."""
+    kind, n, L, _, qnat, _ = WORKLOADS[wl]
+    threads, _ = pick_threads(kind, n, L, qnat)
+    B = CPU_BATCH[wl]
     step = cpu_step_fn(kind, n, L, qnat, B)
-    step()
+    for _ in range(warmup):
+        step()
     ts = []
     for _ in range(steps):
         t0 = time.perf_counter(); step(); ts.append(time.perf_counter() - t0)
     med = statistics.median(ts)
     return {"value": B / med, "unit": "samples/s", "cores": threads, "kind": "port", "batch": B,
+            "pennylane": pennylane_probe(),
             "sample": f"B={B} samples of the same workload per step (complex64 torch, one tensor op per gate, "
-                      f"autograd backward), median of {steps} steps of {med:.2f} s"}
+                      f"autograd backward), median of {steps} steps of {med:.2f} s"}, med
 
 
 def run_reference(args, wl):
@@ -195,28 +220,16 @@ def run_reference(args, wl):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    import torch
-    # bounded sample per step so that warmup + steps end within minutes
-    threads, per_sample = pick_threads(kind, n, L, qnat)
-    budget_s = 150.0 / max(1, args.steps + args.warmup)
-    B = int(min(4096, max(32, min(budget_s, 4.0) / max(per_sample, 1e-6))))
-    B = 1 << (B.bit_length() - 1)
-    step = cpu_step_fn(kind, n, L, qnat, B)
-    for _ in range(args.warmup):
-        step()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step()
-    dt = (time.perf_counter() - t0) / args.steps
-    value = B / dt
+    # the same bounded sample as cpu_baseline; steps capped so that warm-up + steps end within minutes
+    steps = max(1, min(args.steps, 20))
+    cpu, med = time_cpu(wl, steps=steps, warmup=max(1, min(args.warmup, 3)))
+    value = cpu["value"]
     line = {
         "impl": "reference", "metric": "qnn_samples_per_sec_fwd_bwd", "value": value, "unit": "samples/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+        "n_gpus": args.gpus, "steps": steps, "warmup": max(1, min(args.warmup, 3)), "ms_per_step": med * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 (complex64 state)",
-        "data": "synthetic", "config": {"workload": desc, "cpu_sample_batch": B},
-        "cpu_baseline": {"value": value, "unit": "samples/s", "cores": torch.get_num_threads(), "kind": "port",
-                         "sample": f"B={B} per step; PennyLane (the reference's simulator) is not installed, so the "
-                                   "oracle's restatement of its execution model is timed"},
+        "data": "synthetic", "config": {"workload": desc, "name": wl, "cpu_sample_batch": cpu["batch"]},
+        "cpu_baseline": cpu,
         "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -225,94 +238,203 @@ def run_reference(args, wl):
 
 
 # ---- GPU arm ----------------------------------------------------------------------------------------
-def run_b200(args, wl):
-    import torch
-    import torch.distributed as dist
-    import torch.nn.functional as F
+def traffic_record(wl):
+    """DRAM bytes per launch of the dominant kernel as recorded from an `ncu --set full` capture
+    (profiles/traffic.json): NOT measured in this run, and labelled so."""
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        rec = json.load(open(tpath)).get(wl)
+    except Exception:
+        rec = None
+    if not rec:
+        return None, "no ncu capture recorded for this workload"
+    return rec.get("bwd_dram_bytes_per_launch"), "ncu --set full, " + rec.get("source", "profiles/traffic.json") + " (not measured in this run)"
 
+
+class Ctx:
+    """Per-process state shared by the workload measurements."""
+
+    def __init__(self):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device (the product has no CPU path; use --impl reference for the CPU arm)")
+        torch.cuda.set_device(self.local_rank)
+        self.dev = torch.device("cuda", self.local_rank)
+        if self.world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)     # > 126 MB L2
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, ms):
+        t = self.torch.tensor([ms], device=self.dev, dtype=self.torch.float64)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return t.item()
+
+
+def measure_workload(ctx, wl, B, steps, warmup, clocks=None):
+    """Device-timed fwd+bwd step of one workload on inputs resident in HBM; returns the record pieces."""
     import qris_b200
-    from qris_b200.parallel import FlatGradBucket
-
-    kind, n, L, B, qnat, desc = WORKLOADS[wl]
-    if args.batch:
-        B = args.batch
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device (the product has no CPU path; use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+    torch, dist, dev = ctx.torch, ctx.dist, ctx.dev
+    kind, n, L, _, qnat, desc = WORKLOADS[wl]
     lib = qris_b200._lib.lib()
-
     circ = qris_b200.reference_circuit(n, L) if kind == "ref" else qris_b200.u3cu3_circuit(n, L)
     ops = [(o.kind, o.wires, o.params) for o in circ.ops]
     f_fwd, f_bwd = algorithmic_flops(ops, n)
-    torch.manual_seed(1234 + rank)
+    torch.manual_seed(1234 + ctx.rank)
     x = (2 * torch.rand(B, n, device=dev) - 1)
     gout = torch.randn(B, n, device=dev)
     torch.manual_seed(99)
     w = 2 * torch.pi * torch.rand(circ.n_weights, device=dev)
     gw_bucket = torch.zeros(circ.n_weights, device=dev)
     head = qris_b200.QuantumNATHead(sigma=0.01, lo=-2.0, hi=2.0, levels=5).to(dev).train() if qnat else None
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
-    h = circ.handle(local_rank)
+    h = circ.handle(ctx.local_rank)
     launches_per_step = lib.qnn_forward_launches(h, B) + lib.qnn_backward_launches(h, B) + (6 if qnat else 0)
 
     def step():
-        wn = w + 0.01 * torch.randn_like(w) if qnat else w           # weight-space noise (Est:186-188)
-        y, state = qris_b200.qnn_forward_raw(circ, x, wn, save_state=True)   # keeps psi_final for the adjoint pass
-        if qnat:
-            yq = y.detach().requires_grad_(True)
-            out = head(yq)
-            out.backward(gout)
-            gy = yq.grad
-        else:
-            gy = gout
-        gx, _ = qris_b200.qnn_backward_raw(circ, x, wn, gy, need_gx=True, gw_out=gw_bucket, state=state)
-        if world > 1:
-            dist.all_reduce(gw_bucket)
+        with torch.cuda.nvtx.range("bench/step"):
+            wn = w + 0.01 * torch.randn_like(w) if qnat else w           # weight-space noise (Est:186-188)
+            y, state = qris_b200.qnn_forward_raw(circ, x, wn, save_state=True)   # keeps psi_final for the adjoint pass
+            if qnat:
+                yq = y.detach().requires_grad_(True)
+                out = head(yq)
+                out.backward(gout)
+                gy = yq.grad
+            else:
+                gy = gout
+            gx, _ = qris_b200.qnn_backward_raw(circ, x, wn, gy, need_gx=True, gw_out=gw_bucket, state=state)
+            if ctx.world > 1:
+                with torch.cuda.nvtx.range("allreduce/gw"):
+                    dist.all_reduce(gw_bucket)
         return gx
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
+    for _ in range(max(warmup, 3)):
+        step()
+    ctx.barrier()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    ctx.barrier()
+    if clocks is not None:
+        clocks.mark()
+    for s_, e_ in ev:
+        ctx.flush.zero_()                                             # L2 flush, outside the timed events
+        s_.record(); step(); e_.record()
+    ctx.barrier()
+    if clocks is not None:
+        clocks.mark()
+    total_ms = ctx.max_over_ranks(sum(s_.elapsed_time(e_) for s_, e_ in ev))
+    ms_per_step = total_ms / steps
+    # dominant kernel (adjoint backward) and the forward kernel, timed alone on the same stream
+    gy_fixed = torch.randn(B, n, device=dev)
+    k_bwd, k_fwd = [], []
+    for _ in range(max(5, min(steps, 20))):
+        ctx.flush.zero_()
+        s1, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s2.record(); _, st_k = qris_b200.qnn_forward_raw(circ, x, w, save_state=True); e2.record()
+        s1.record(); qris_b200.qnn_backward_raw(circ, x, w, gy_fixed, need_gx=True, gw_out=gw_bucket, state=st_k); e1.record()
         torch.cuda.synchronize()
+        k_bwd.append(s1.elapsed_time(e1)); k_fwd.append(s2.elapsed_time(e2))
+    bwd_ms, fwd_ms = statistics.mean(k_bwd), statistics.mean(k_fwd)
+    achieved = f_bwd * B / (bwd_ms * 1e-3) / 1e12
+    traffic, traffic_source = traffic_record(wl)
+    step_tf = (f_fwd + f_bwd) * B / (ms_per_step * 1e-3) / 1e12
+    roofline = {
+        "bound": "fp32", "kernel": "qnn_backward_saved (adjoint VJP from the saved final state: uncompute + gradients)",
+        "achieved": achieved, "peak": FP32_PEAK_NOMINAL_TFLOPS, "unit": "TFLOP/s",
+        "frac": achieved / FP32_PEAK_NOMINAL_TFLOPS,
+        "peak_source": "nominal 148 SM x 128 lanes x 2 x 1.965 GHz (MEASURED_PEAKS.json has no FP32 entry)",
+        "traffic": traffic, "traffic_source": traffic_source,
+        "algorithmic_flops_per_sample": {"fwd": f_fwd, "bwd": f_bwd},
+        "kernel_ms": {"bwd": bwd_ms, "fwd": fwd_ms},
+        "fwd_achieved": f_fwd * B / (fwd_ms * 1e-3) / 1e12,
+        "step_achieved": step_tf, "step_frac": step_tf / FP32_PEAK_NOMINAL_TFLOPS,
+        "hbm_gbs": hbm_bytes_per_sample(n) * B / (ms_per_step * 1e-3) / 1e9,
+        "saved_state_bytes_per_outstanding_forward": int(lib.qnn_state_bytes(h, B)),
+    }
+    return {"circ": circ, "value": B * ctx.world / (ms_per_step * 1e-3), "ms_per_step": ms_per_step, "roofline": roofline,
+            "launches_per_step": launches_per_step, "head": head, "desc": desc, "n": n, "L": L,
+            "plan": lib.qnn_circuit_plan(h, B).decode()}
 
-    with ClockSampler(local_rank) as clocks:                          # started early: nvidia-smi needs a moment
-        for _ in range(max(args.warmup, 3)):
-            step()
-        barrier()
-        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-        barrier()
-        clocks.mark()
-        for s, e in ev:
-            flush.zero_()                                             # L2 flush, outside the timed events
-            s.record(); step(); e.record()
-        barrier()
-        clocks.mark()
-        step_ms = [s.elapsed_time(e) for s, e in ev]
-        total_ms = sum(step_ms)
-        # dominant kernel (adjoint backward) and the forward kernel, timed alone on the same stream
-        gy_fixed = torch.randn(B, n, device=dev)
-        k_bwd, k_fwd = [], []
-        for _ in range(max(5, min(args.steps, 20))):
-            flush.zero_()
-            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            s2.record(); _, st_k = qris_b200.qnn_forward_raw(circ, x, w, save_state=True); e2.record()
-            s.record(); qris_b200.qnn_backward_raw(circ, x, w, gy_fixed, need_gx=True, gw_out=gw_bucket, state=st_k); e.record()
-            torch.cuda.synchronize()
-            k_bwd.append(s.elapsed_time(e)); k_fwd.append(s2.elapsed_time(e2))
-    t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms = t.item()
-    ms_per_step = total_ms / args.steps
-    value = B * world / (ms_per_step * 1e-3)
+
+def secondary_record(ctx, wl, B, steps, scaling, name=None):
+    m = measure_workload(ctx, wl, B, steps, 3)
+    r = m["roofline"]
+    return {"name": name or wl, "workload": m["desc"], "metric": "qnn_samples_per_sec_fwd_bwd", "value": m["value"],
+            "unit": "samples/s", "n_gpus": ctx.world, "steps": steps, "ms_per_step": m["ms_per_step"], "scaling": scaling,
+            "batch_per_gpu": B, "global_batch": B * ctx.world, "plan": m["plan"],
+            "roofline": {k: r[k] for k in ("bound", "achieved", "peak", "unit", "frac", "step_frac", "step_achieved", "kernel_ms",
+                                           "algorithmic_flops_per_sample", "traffic", "traffic_source")}}
+
+
+def cfg1_record(ctx, steps=30):
+    """BASELINE configs[0], the step the reference ships (Run:341-369): nine forwards of 256 samples (n=6, L=3),
+    one backward, pruning off, AdamW -- through runner.qsc_step on device-resident synthetic data; eager, with
+    the nine users concatenated, and each of those replayed as a CUDA graph.  Host-timed around a device
+    synchronise (the step is host-bound when eager), single process."""
+    import qris_b200
+    from qris_b200 import estimators as E
+    from qris_b200 import optim, runner
+    torch = ctx.torch
+    r = runner.Y2HRunner(data_len=2560, batch_size_DML=256, device=ctx.dev, verbose=False)
+    loader, _ = r.get_dataloader_DML()
+    batches = [b for b in loader if b[0][0][0].shape[0] == 256]
+    circ = qris_b200.reference_circuit(6, 3)
+    f_fwd, f_bwd = algorithmic_flops([(o.kind, o.wires, o.params) for o in circ.ops], 6)
+    modes = {}
+    for concat, graph in ((False, False), (True, False), (False, True), (True, True)):
+        torch.manual_seed(0)
+        model = E.QSC_P128(use_quantumnat=False, use_gradient_pruning=False).to(ctx.dev).train()
+        opt = optim.FlatPrunedAdamW(model.parameters(), lr=1e-3, weight_decay=0.01, device_step_count=graph)
+        step = runner.GraphedQSCStep(r, model, opt, concat) if graph else (lambda b: r.qsc_step(model, opt, b, concat))
+        for b in batches[:6]:
+            step(b)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(steps):
+            step(batches[i % len(batches)])
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / steps
+        key = ("graph" if graph else "eager") + ("_concat_users" if concat else "")
+        sps = 9 * 256 / dt
+        modes[key] = {"steps_per_s": 1.0 / dt, "samples_per_s": sps, "ms_per_step": dt * 1e3,
+                      "qnn_frac_of_fp32_roofline": (f_fwd + f_bwd) * sps / 1e12 / FP32_PEAK_NOMINAL_TFLOPS}
+    return {"name": "cfg1", "workload": "BASELINE configs[0]: the as-shipped training step (Run:341-369): QSC_P128 n=6 L=3, nine "
+                                        "user batches of 256, one backward, AdamW; whole model (CNN front end + QNN + classifier + optimiser)",
+            "metric": "qsc_optimiser_steps_per_sec", "unit": "steps/s", "n_gpus": 1, "steps": steps, "scaling": "none",
+            "value": modes["eager"]["steps_per_s"], "modes": modes,
+            "roofline": {"bound": "launch/host (71.0 kflop per sample: SURVEY.md H5)", "unit": "TFLOP/s", "peak": FP32_PEAK_NOMINAL_TFLOPS,
+                         "frac": modes["graph_concat_users"]["qnn_frac_of_fp32_roofline"],
+                         "algorithmic_flops_per_sample": {"fwd": f_fwd, "bwd": f_bwd}}}
+
+
+def run_b200(args, wl):
+    import torch
+    import torch.nn.functional as F
+
+    import qris_b200
+    from qris_b200.parallel import FlatGradBucket
+
+    ctx = Ctx()
+    dist, dev, world, rank = ctx.dist, ctx.dev, ctx.world, ctx.rank
+    kind, n, L, B, qnat, desc = WORKLOADS[wl]
+    if args.batch:
+        B = args.batch
+    lib = qris_b200._lib.lib()
+    with ClockSampler(ctx.local_rank) as clocks:                      # started early: nvidia-smi needs a moment
+        m = measure_workload(ctx, wl, B, args.steps, args.warmup, clocks)
+    circ, head, ms_per_step, value = m["circ"], m["head"], m["ms_per_step"], m["value"]
+    launches_per_step = m["launches_per_step"]
+    flush, barrier = ctx.flush, ctx.barrier
 
     # ---- end to end through the module surface: pinned host -> device, loss read back ----
     torch.manual_seed(5)
@@ -350,10 +472,19 @@ def run_b200(args, wl):
         flush.zero_()
         s.record(); e2e_step(); e.record()
     barrier()
-    t = torch.tensor([sum(s.elapsed_time(e) for s, e in ev)], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = B * world / (t.item() / args.steps * 1e-3)
+    e2e_ms = ctx.max_over_ranks(sum(s.elapsed_time(e) for s, e in ev))
+    e2e_value = B * world / (e2e_ms / args.steps * 1e-3)
+
+    # ---- secondary records: every other number the documentation quotes (all ranks take part) ----
+    secondary = []
+    if not args.no_secondary and wl == "cfg3" and not args.batch:
+        if world > 1:     # BASELINE configs[2] as stated: batch 65,536 GLOBAL, split over the N GPUs
+            secondary.append(secondary_record(ctx, "cfg3", WORKLOADS["cfg3"][3] // world, max(5, min(args.steps, 20)), "strong",
+                                              name="cfg3_strong"))
+        secondary.append(secondary_record(ctx, "cfg4", WORKLOADS["cfg4"][3], 5, "weak"))
+        secondary.append(secondary_record(ctx, "cfg2", WORKLOADS["cfg2"][3], max(5, min(args.steps, 20)), "weak"))
+        if world == 1:
+            secondary.append(cfg1_record(ctx))
 
     if rank == 0:
         tf = 0.0
@@ -364,16 +495,10 @@ def run_b200(args, wl):
                 tf = val.value
         except Exception:
             pass
-        bwd_ms, fwd_ms = statistics.mean(k_bwd), statistics.mean(k_fwd)
-        achieved = f_bwd * B / (bwd_ms * 1e-3) / 1e12
-        traffic = None
-        tpath = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tpath):
-            try:
-                traffic = json.load(open(tpath)).get(wl, {}).get("bwd_dram_bytes_per_launch")
-            except Exception:
-                traffic = None
-        cpu = time_cpu(kind, n, L, qnat) if (world == 1 and not args.no_cpu) else None
+        roofline = m["roofline"]
+        roofline["peak_measured"] = tf
+        roofline["frac_of_measured"] = (roofline["achieved"] / tf) if tf else None
+        cpu = time_cpu(wl)[0] if (world == 1 and not args.no_cpu) else None
         line = {
             "metric": "qnn_samples_per_sec_fwd_bwd", "value": value, "unit": "samples/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
@@ -382,24 +507,13 @@ def run_b200(args, wl):
             "config": {"workload": desc, "name": wl, "n_qubits": n, "n_layers": L, "batch_per_gpu": B,
                        "global_batch": B * world, "parallelism": f"dp{world}",
                        "l2": "flushed between timed steps (256 MiB memset, outside the per-step CUDA events)",
-                       "plan": lib.qnn_circuit_plan(h, B).decode()},
+                       "plan": m["plan"]},
             "clocks": clocks.summary(),
             "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": xh.numel() * 4 + lh.numel() * 8,
                     "d2h_bytes_per_step": 4},
             "gpu_launches": launches_per_step * args.steps + e2e_launches * args.steps,
-            "roofline": {
-                "bound": "fp32", "kernel": "qnn_backward_saved (adjoint VJP from the saved final state: uncompute + gradients)",
-                "achieved": achieved, "peak": FP32_PEAK_NOMINAL_TFLOPS, "unit": "TFLOP/s",
-                "frac": achieved / FP32_PEAK_NOMINAL_TFLOPS,
-                "peak_source": "nominal 148 SM x 128 lanes x 2 x 1.965 GHz (MEASURED_PEAKS.json has no FP32 entry)",
-                "peak_measured": tf, "frac_of_measured": (achieved / tf) if tf else None,
-                "traffic": traffic, "algorithmic_flops_per_sample": {"fwd": f_fwd, "bwd": f_bwd},
-                "kernel_ms": {"bwd": bwd_ms, "fwd": fwd_ms},
-                "fwd_achieved": f_fwd * B / (fwd_ms * 1e-3) / 1e12,
-                "step_achieved": (f_fwd + f_bwd) * B / (ms_per_step * 1e-3) / 1e12,
-                "step_frac": (f_fwd + f_bwd) * B / (ms_per_step * 1e-3) / 1e12 / FP32_PEAK_NOMINAL_TFLOPS,
-                "hbm_gbs": hbm_bytes_per_sample(n) * B / (ms_per_step * 1e-3) / 1e9,
-            },
+            "roofline": roofline,
+            "secondary": secondary,
         }
         if cpu is not None:
             line["cpu_baseline"] = cpu
@@ -427,6 +541,7 @@ def main():
     ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
     ap.add_argument("--batch", type=int, default=0, help="override the per-GPU batch")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the secondary records (cfg4, cfg2, cfg1, strong scaling)")
     args = ap.parse_args()
     # The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version line at the
     # first communicator), so everything but the result line is sent to stderr: fd 1 is pointed at fd 2 for

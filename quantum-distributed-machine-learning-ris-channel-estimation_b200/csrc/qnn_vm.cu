@@ -48,9 +48,13 @@ size_t smem_bytes(const Program& p, int n_inputs, int warps, bool bwd, bool clus
 }
 
 // ---- per-call tables: gate coefficients (double-precision trig) and merged diagonals -----------------
-__global__ void k_vm_prep(const DevOp* __restrict__ coef_ops, int n_coef, const DiagDesc* __restrict__ diags, int n_diags,
-                          const DiagTerm* __restrict__ terms, const float* __restrict__ w, int tb, int wbits, float* __restrict__ coef,
-                          float2* __restrict__ big, float2* __restrict__ small, int coef_blocks) {
+// Grid: coef_blocks CTAs for the coefficient rows, then `chunks` CTAs per diagonal, each filling kPrepChunk
+// entries of its table (a 16-qubit table has 65,536 entries: one CTA per table took ~0.9 ms per call).
+constexpr int kPrepThreads = 128, kPrepChunk = 1024, kPrepTermTile = 64;
+__global__ void __launch_bounds__(kPrepThreads)
+k_vm_prep(const DevOp* __restrict__ coef_ops, int n_coef, const DiagDesc* __restrict__ diags, int n_diags,
+          const DiagTerm* __restrict__ terms, const float* __restrict__ w, int tb, int wbits, float* __restrict__ coef,
+          float2* __restrict__ big, float2* __restrict__ small, int coef_blocks, int chunks) {
   if ((int)blockIdx.x < coef_blocks) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_coef) return;
@@ -73,28 +77,53 @@ __global__ void k_vm_prep(const DevOp* __restrict__ coef_ops, int n_coef, const 
     row[4] = (float)cl; row[5] = (float)sl; row[6] = (float)cp; row[7] = (float)sp;
     return;
   }
-  const int d = blockIdx.x - coef_blocks;
+  const int d = ((int)blockIdx.x - coef_blocks) / chunks, chunk = ((int)blockIdx.x - coef_blocks) % chunks;
   if (d >= n_diags) return;
   const DiagDesc D = diags[d];
   const int G = 32 << wbits;
   const int entries = D.is_reg ? 32 : 32 * G;
+  if (chunk * kPrepChunk >= entries) return;
   const unsigned tmask = wbits ? (unsigned)(G - 1) : ((1u << tb) - 1u);   // thread bits of one sample
-  for (int e = threadIdx.x; e < entries; e += blockDim.x) {
-    const int j = D.is_reg ? e : (e / G), t = D.is_reg ? 0 : (e % G);
-    const unsigned p = (unsigned)j | (((unsigned)t & tmask) << kR);
-    double ang = 0.0;
-    for (int t = 0; t < D.n_terms; ++t) {
-      const DiagTerm tm = terms[D.first_term + t];
-      if (tm.kind == 0) {
-        const double phi = (tm.src == QNN_SRC_CONST) ? (double)tm.value : (double)w[tm.src];
-        ang += ((p >> tm.bit0) & 1u) ? 0.5 * phi : -0.5 * phi;
-      } else if (((p >> tm.bit0) & 1u) && ((p >> tm.bit1) & 1u)) {
-        ang += tm.kind == 1 ? 3.14159265358979323846 : ((tm.src == QNN_SRC_CONST) ? (double)tm.value : (double)w[tm.src]);
-      }
+  // the terms of this diagonal, staged once per CTA: angle (the weight read happens here) and bit masks
+  __shared__ double s_phi[kPrepTermTile];
+  __shared__ unsigned s_m0[kPrepTermTile], s_m1[kPrepTermTile];
+  __shared__ int s_kind[kPrepTermTile];
+  constexpr int kPer = kPrepChunk / kPrepThreads;
+  double ang[kPer];
+#pragma unroll
+  for (int q = 0; q < kPer; ++q) ang[q] = 0.0;
+  for (int t0 = 0; t0 < D.n_terms; t0 += kPrepTermTile) {
+    const int nt = min(kPrepTermTile, D.n_terms - t0);
+    __syncthreads();
+    if ((int)threadIdx.x < nt) {
+      const DiagTerm tm = terms[D.first_term + t0 + threadIdx.x];
+      const double v = (tm.src == QNN_SRC_CONST) ? (double)tm.value : (double)w[tm.src];
+      s_kind[threadIdx.x] = tm.kind;
+      s_phi[threadIdx.x] = tm.kind == 0 ? 0.5 * v : (tm.kind == 1 ? 3.14159265358979323846 : v);
+      s_m0[threadIdx.x] = 1u << tm.bit0;
+      s_m1[threadIdx.x] = tm.kind == 0 ? 0u : (1u << tm.bit1);
     }
-    double s, c;
-    sincos(ang, &s, &c);
-    const float2 v = make_float2((float)c, (float)s);
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < kPer; ++q) {
+      const int e = chunk * kPrepChunk + q * kPrepThreads + threadIdx.x;
+      const int j = D.is_reg ? e : (e / G), t = D.is_reg ? 0 : (e % G);
+      const unsigned p = (unsigned)j | (((unsigned)t & tmask) << kR);
+      double acc = ang[q];
+      for (int k = 0; k < nt; ++k) {
+        if (s_kind[k] == 0) acc += (p & s_m0[k]) ? s_phi[k] : -s_phi[k];
+        else if ((p & s_m0[k]) && (p & s_m1[k])) acc += s_phi[k];
+      }
+      ang[q] = acc;
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < kPer; ++q) {
+    const int e = chunk * kPrepChunk + q * kPrepThreads + threadIdx.x;
+    if (e >= entries) continue;
+    double sn, cs;
+    sincos(ang[q], &sn, &cs);
+    const float2 v = make_float2((float)cs, (float)sn);
     if (D.is_reg) small[(size_t)D.table * 32 + e] = v; else big[(size_t)D.table * 32 * G + e] = v;
   }
 }
@@ -157,12 +186,13 @@ void fill_args(const qnn_circuit* c, const Program& p, const Plan& pl, void* ws,
 }
 
 int launch_prep(const Program& p, const float* w, const VmArgs& a, cudaStream_t st) {
-  const int coef_blocks = ((int)p.coef_ops.size() + 127) / 128;
-  const int blocks = coef_blocks + (int)p.diags.size();
+  const int coef_blocks = ((int)p.coef_ops.size() + kPrepThreads - 1) / kPrepThreads;
+  const int chunks = p.n_big_tables > 0 ? std::max(1, (1024 << p.wb) / kPrepChunk) : 1;   // CTAs per diagonal table
+  const int blocks = coef_blocks + (int)p.diags.size() * chunks;
   if (blocks == 0) return QNN_OK;
-  k_vm_prep<<<blocks, 128, 0, st>>>(p.d_coef_ops, (int)p.coef_ops.size(), p.d_diags, (int)p.diags.size(), p.d_terms, w, p.tb, p.wb,
-                                    const_cast<float*>(a.coef), const_cast<float2*>(a.big), const_cast<float2*>(a.small),
-                                    coef_blocks);
+  k_vm_prep<<<blocks, kPrepThreads, 0, st>>>(p.d_coef_ops, (int)p.coef_ops.size(), p.d_diags, (int)p.diags.size(), p.d_terms, w, p.tb,
+                                             p.wb, const_cast<float*>(a.coef), const_cast<float2*>(a.big),
+                                             const_cast<float2*>(a.small), coef_blocks, chunks);
   QNN_CUDA_CHECK(cudaGetLastError());
   return QNN_OK;
 }

@@ -60,12 +60,22 @@ class FlatGradBucket:
         ``local_rows``: this rank's number of samples when shards are NOT equal (ragged tail of
         ``shard_range``, last batch of an epoch).  Each rank's mean-loss gradient is then weighted by its
         row count and the sum divided by the global count, which travels in the same collective (no host
-        round trip): the result is the gradient of the mean over the global batch whatever the split."""
+        round trip): the result is the gradient of the mean over the global batch whatever the split.
+        That holds for models whose samples are independent.  Where the forward couples samples of different
+        ranks (``QuantumNATHead(process_group=...)``: shared batch statistics), scale the loss by the global
+        row count on every rank instead (``sum / B_global``) and call ``all_reduce(average=False)``."""
         if not (dist.is_available() and dist.is_initialized()):
             return
         world = dist.get_world_size(group)
         if world == 1:
             return
+        if self.flat.is_cuda:
+            with torch.cuda.nvtx.range("allreduce/flat-gradient-bucket"):
+                self._all_reduce(group, average, local_rows, world)
+        else:
+            self._all_reduce(group, average, local_rows, world)
+
+    def _all_reduce(self, group, average, local_rows, world) -> None:
         if local_rows is not None and average:
             self.flat.mul_(float(local_rows))
             self._buf[-1] = float(local_rows)

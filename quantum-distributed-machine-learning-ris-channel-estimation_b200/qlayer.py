@@ -45,7 +45,7 @@ def qnn_forward_raw(circuit: Circuit, x: torch.Tensor, w: torch.Tensor, save_sta
     dev = x.device.index if x.device.index is not None else torch.cuda.current_device()
     h = circuit.handle(dev)
     state = None
-    with torch.cuda.device(dev):
+    with torch.cuda.device(dev), torch.cuda.nvtx.range("qnn/forward"):
         ws = _workspace(lib.qnn_forward_workspace_bytes(h, B), x.device)
         st = torch.cuda.current_stream(dev).cuda_stream
         nbytes = lib.qnn_state_bytes(h, B) if save_state else 0
@@ -76,7 +76,7 @@ def qnn_backward_raw(circuit: Circuit, x: torch.Tensor, w: torch.Tensor, gy: tor
         return gx, gw
     dev = x.device.index if x.device.index is not None else torch.cuda.current_device()
     h = circuit.handle(dev)
-    with torch.cuda.device(dev):
+    with torch.cuda.device(dev), torch.cuda.nvtx.range("qnn/backward"):
         ws = _workspace(lib.qnn_backward_workspace_bytes(h, B), x.device)
         st = torch.cuda.current_stream(dev).cuda_stream
         if state is not None:

@@ -42,7 +42,7 @@ class _QnatFunction(torch.autograd.Function):
         sums = torch.zeros(2 * n + 1, dtype=torch.float64, device=yc.device)
         B_total = B
         nz = None if noise is None else noise.detach().to(torch.float32).contiguous()
-        with torch.cuda.device(dev):
+        with torch.cuda.device(dev), torch.cuda.nvtx.range("quantumnat/forward"):
             st = torch.cuda.current_stream(dev).cuda_stream
             if cfg["normalise"]:
                 ws = _workspace(lib.qnat_workspace_bytes(B, n), yc.device)
@@ -69,7 +69,7 @@ class _QnatFunction(torch.autograd.Function):
         bsums = torch.zeros(2 * n + 1, dtype=torch.float64, device=yc.device)
         dev = yc.device.index
         p = ctx.p
-        with torch.cuda.device(dev):
+        with torch.cuda.device(dev), torch.cuda.nvtx.range("quantumnat/backward"):
             st = torch.cuda.current_stream(dev).cuda_stream
             if p.normalise:
                 ws = _workspace(lib.qnat_workspace_bytes(B, n), yc.device)

@@ -73,8 +73,10 @@ def qnat_global_statistics(rank, world, dev, B):
 
 
 def module_level(rank, world, dev, B):
-    """QSC_QuantumNAT (config 3's model) for one step: flat gradient bucket after the all-reduce, weighted by row
-    counts, == the single-GPU gradient of the global-batch mean loss."""
+    """QSC_QuantumNAT (config 3's model, batch statistics shared across ranks) for one step == the single-GPU
+    gradient of the global-batch mean loss.  The head's backward couples samples of different ranks, so every
+    rank scales its loss by the GLOBAL row count (sum / B) and the bucket is summed, not averaged; this holds
+    for ragged shards too."""
     torch.manual_seed(3)
     single = E.QSC_QuantumNAT(n_qubits=10, n_layers=2, noise_level=0.0, act_noise=0.0).to(dev).train()
     torch.manual_seed(3)
@@ -86,12 +88,34 @@ def module_level(rank, world, dev, B):
     F.nll_loss(single(x), lab).backward()
     lo, hi = shard_range(B, rank, world)
     b2 = FlatGradBucket(shared.parameters()); b2.zero()
-    F.nll_loss(shared(x[lo:hi]), lab[lo:hi]).backward()
-    b2.all_reduce(local_rows=hi - lo)
+    (F.nll_loss(shared(x[lo:hi]), lab[lo:hi], reduction="sum") / B).backward()
+    b2.all_reduce(average=False)
     # away from quantiser edges the two graphs are the same function; allow the few samples whose bin flipped
     err = (b2.flat - b1.flat).abs().max() / b1.flat.abs().max()
     assert float(err) < 5e-4, f"module-level gradient differs: {float(err):.3e}"
-    say(rank, f"module-level QSC_QuantumNAT step: B={B}, max|dg|/max|g| = {float(err):.2e}")
+    say(rank, f"module-level QSC_QuantumNAT step: B={B} ({hi - lo} rows here), max|dg|/max|g| = {float(err):.2e}")
+
+
+def module_level_row_weighted(rank, world, dev, B):
+    """QSC_P128 (the reference's model: no batch statistics) with per-shard MEAN losses on ragged shards: the
+    bucket weights each rank by its row count (``local_rows``) and reproduces the global-batch mean gradient."""
+    torch.manual_seed(4)
+    single = E.QSC_P128(use_quantumnat=False, use_gradient_pruning=False).to(dev).train()
+    shared = E.QSC_P128(use_quantumnat=False, use_gradient_pruning=False).to(dev).train()
+    shared.load_state_dict(single.state_dict())
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn(B, 2, 16, 8, generator=g).to(dev)
+    lab = torch.randint(0, 3, (B,), generator=g).to(dev)
+    b1 = FlatGradBucket(single.parameters()); b1.zero()
+    F.nll_loss(single(x), lab).backward()
+    lo, hi = shard_range(B, rank, world)
+    b2 = FlatGradBucket(shared.parameters()); b2.zero()
+    F.nll_loss(shared(x[lo:hi]), lab[lo:hi]).backward()
+    b2.all_reduce(local_rows=hi - lo)
+    err = (b2.flat - b1.flat).abs().max() / b1.flat.abs().max()
+    assert float(err) < 2e-5, f"row-weighted gradient differs: {float(err):.3e}"
+    say(rank, f"module-level QSC_P128 step, row-weighted mean of ragged shards: B={B} ({hi - lo} rows here), "
+              f"max|dg|/max|g| = {float(err):.2e}")
 
 
 def runner_under_torchrun(rank, world, dev):
@@ -124,6 +148,7 @@ def main():
         qnat_global_statistics(rank, world, dev, 4097)
         module_level(rank, world, dev, 510)
         module_level(rank, world, dev, 257)
+        module_level_row_weighted(rank, world, dev, 771)
         runner_under_torchrun(rank, world, dev)
         say(rank, "all checks passed")
     finally:
