@@ -49,8 +49,10 @@ class FlatPrunedAdamW:
     def zero_grad(self) -> None:
         self.bucket.zero()
 
-    def step(self) -> None:
-        self.bucket.all_reduce(group=self.process_group)
+    def step(self, local_rows: Optional[int] = None) -> None:
+        """``local_rows``: this rank's sample count for the step when data-parallel shards may be unequal (the
+        last batch of an epoch): the bucket then averages weighted by rows (``FlatGradBucket.all_reduce``)."""
+        self.bucket.all_reduce(group=self.process_group, local_rows=local_rows)
         self.t += 1
         dev = self.flat.device.index
         thr = -1.0 if self.prune_threshold is None else float(self.prune_threshold)

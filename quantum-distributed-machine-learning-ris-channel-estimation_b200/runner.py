@@ -80,6 +80,18 @@ class GraphedQSCStep:
         return self.loss
 
 
+def can_concat_users(model) -> bool:
+    """Whether the nine user batches of one step may run as ONE model call with the same result: the model must
+    treat samples independently (no batch statistics: BatchNorm in training mode, QuantumNATHead) and must not
+    draw per-call randomness (the weight noise of Est:176-196 is drawn once per call, so nine calls see nine
+    draws)."""
+    from .qnat import QuantumNATHead
+    for m in model.modules():
+        if isinstance(m, (torch.nn.modules.batchnorm._BatchNorm, QuantumNATHead)):
+            return False
+    return not (getattr(model, "use_quantumnat", False) and getattr(model, "noise_level", 0.0) > 0)
+
+
 class Y2HRunner:
     def __init__(self, Pilot_num=128, data_len=20000, SNRdb=10, batch_size_DML=256, lr=1e-3, n_epochs=100,
                  device=None, seed=0, workdir="./workspace", n_qubits=6, n_layers=3, verbose=True):
@@ -121,7 +133,7 @@ class Y2HRunner:
             outputs = model(D.pilot_image(yp, self.Pilot_num))
             loss = F.nll_loss(outputs, torch.clamp(ind.long().reshape(-1), 0, outputs.size(-1) - 1))
             loss.backward()
-            opt.step()
+            opt.step(local_rows=ind.numel() if self.world > 1 else None)
             return loss.detach()
         loss = 0
         for sid in range(3):
@@ -131,13 +143,17 @@ class Y2HRunner:
                 labels = torch.clamp(ind.long().reshape(-1), 0, outputs.size(-1) - 1)  # Run:346-360
                 loss = loss + F.nll_loss(outputs, labels) / 9                          # Run:362
         loss.backward()                                                               # Run:364
-        opt.step()                                                                    # Run:367-369 (prune + AdamW)
+        rows = sum(sutd[s][u][3].numel() for s in range(3) for u in range(3))
+        opt.step(local_rows=rows if self.world > 1 else None)                         # Run:367-369 (prune + AdamW)
         return loss.detach()
 
     def train_QSC_P128(self, n_epochs: Optional[int] = None, use_quantumnat=False, use_gradient_pruning=False,
-                       max_iters_per_epoch: Optional[int] = None, save=True, concat_users=False,
+                       max_iters_per_epoch: Optional[int] = None, save=True, concat_users: Optional[bool] = None,
                        cuda_graph=False) -> Dict[str, list]:
-        """``cuda_graph``: record one optimiser step (nine forwards, backward, prune + AdamW) into a CUDA graph
+        """``concat_users``: run the nine user batches of a step as one model call (``qsc_step``); the default
+        ``None`` does so whenever that gives the same result (``can_concat_users``: no batch statistics, no
+        per-call weight noise) -- 6.5x fewer kernel launches per step at the reference's sizes.
+        ``cuda_graph``: record one optimiser step (nine forwards, backward, prune + AdamW) into a CUDA graph
         after three eager steps and replay it for every later batch of the same shape (single process only;
         see ``GraphedQSCStep``)."""
         torch.manual_seed(self.seed)
@@ -147,6 +163,8 @@ class Y2HRunner:
         opt = FlatPrunedAdamW(model.parameters(), lr=self.lr, weight_decay=0.01,        # Run:320
                               prune_threshold=model.gradient_threshold if use_gradient_pruning else None,
                               device_step_count=bool(cuda_graph))
+        if concat_users is None:
+            concat_users = can_concat_users(model)
         graphed = GraphedQSCStep(self, model, opt, concat_users) if cuda_graph and self.world == 1 else None
         train_loader, val_loader = self.get_dataloader_DML()
         self.log("Data Loaded for QSC with QuantumNAT + On-chip QNN optimization!")

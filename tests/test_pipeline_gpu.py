@@ -179,8 +179,11 @@ def test_routed_nmse_parity_kernel_vs_oracle():
     assert all(np.isfinite(res["LS"]))
 
 
-@pytest.mark.parametrize("pilot", [32, 64, 256])
+@pytest.mark.parametrize("pilot", [32, 64, 128, 256])
 def test_pilot_length_variants(pilot):
+    """BASELINE config 5 at small scale, for every pilot length of the sweep: shapes and gradients, then a short
+    training run and the routed NMSE-vs-SNR evaluation with the kernel-backed and the oracle-backed classifier:
+    NMSE within 0.05 dB, identical accuracy (profiles/cfg5_sweep.py is the full-size run)."""
     hw = D.pilot_shape(pilot)
     model = E.QSC_P128(use_quantumnat=False, use_gradient_pruning=False, pilot_hw=hw).cuda()
     gen = D.SyntheticRIS(pilot, seed=1, device="cuda")
@@ -189,6 +192,19 @@ def test_pilot_length_variants(pilot):
     assert out.shape == (24, 3)
     F.nll_loss(out, ind).backward()
     assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in model.parameters())
+    r = runner.Y2HRunner(Pilot_num=pilot, data_len=600, batch_size_DML=50, n_epochs=2, lr=5e-3, device="cuda", verbose=False)
+    r.train_QSC_P128(save=False)
+    r.train_Conv_Linear_of_HDCE(n_epochs=1, max_iters_per_epoch=4)
+    twin = oracle_twin(r.model_QSC).eval()
+
+    class OracleClassifier(torch.nn.Module):
+        def forward(self, img):
+            with torch.no_grad():
+                return twin(img.cpu().double()).float().cuda()
+    res = evaluate.snr_sweep(D.SyntheticRIS(pilot, seed=0, device="cuda"), {"quantum": r.model_QSC, "quantum_oracle": OracleClassifier()},
+                             r.convs, r.fc, snrs=(5, 15), n_per_pair=40, batch=40)
+    assert all(abs(a - b) < 0.05 for a, b in zip(res["quantum"], res["quantum_oracle"]))
+    assert res["acc_quantum"] == res["acc_quantum_oracle"] and all(np.isfinite(res["LS"]))
 
 
 def test_concatenated_users_step_equals_nine_way_step():
