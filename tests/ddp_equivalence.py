@@ -138,6 +138,10 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # cuDNN's TF32 convolutions (torch's default) round differently for different batch shapes; the comparison
+    # of a shard with the whole batch is about the data-parallel arithmetic, so keep the classical front end in fp32
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     dist.init_process_group("nccl", device_id=dev)
     try:
