@@ -38,10 +38,10 @@ size_t table_bytes(const Program& p, int n_inputs, int warps, bool bwd, bool clu
 // exchange buffers (8 KB per warp, each group's aligned to its size) + worst-case alignment gap + tables;
 // the cluster geometry keeps its exchange buffer in the workspace
 size_t smem_bytes(const Program& p, int n_inputs, int warps, bool bwd, bool cluster) {
-  if (cluster) {   // + alignment gap + the 64 KB buffer of the local exchanges, when the program has any
-    bool has_local = false;
-    for (const Exchange& X : p.exchanges) has_local = has_local || X.pad[0] != 0;
-    return table_bytes(p, n_inputs, warps, bwd, true) + (has_local ? 2 * 65536 : 0) + 64;
+  if (cluster) {   // + the two 64 KB buffers of the shared-memory exchanges (local and across CTAs), when the program has any
+    bool has_shared = false;
+    for (const Exchange& X : p.exchanges) has_shared = has_shared || X.pad[0] != 0;
+    return table_bytes(p, n_inputs, warps, bwd, true) + (has_shared ? 2 * 65536 : 0) + 64;
   }
   const size_t group_buf = (size_t)8192 << p.wb;
   return group_buf + (size_t)warps * 8192 + table_bytes(p, n_inputs, warps, bwd, false) + 64;
@@ -181,7 +181,7 @@ void fill_args(const qnn_circuit* c, const Program& p, const Plan& pl, void* ws,
   if (pl.cluster > 0) {
     unsigned char* cb = wsb + pl.ws_coef + pl.ws_diag + pl.ws_partial;
     a->cbuf = cb;
-    a->cred = reinterpret_cast<float*>(cb + ((size_t)pl.n_clusters << (p.n + 5)));
+    a->cred = reinterpret_cast<float*>(cb + pl.ws_cbuf);
   }
 }
 
@@ -212,7 +212,7 @@ bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
   if (!p.ok) return false;
   const int bwd_warps = kBwdThreads / 32;
   const int n_ang_in = p.amplitude ? 0 : c->n_inputs;        // input columns that need per-warp scratch
-  out->cluster = 0; out->n_clusters = 0; out->ws_cluster = 0;
+  out->cluster = 0; out->n_clusters = 0; out->ws_cluster = 0; out->ws_cbuf = 0;
   out->threads = kBwdThreads;
   out->warps_per_cta = bwd_warps;
   if ((1 << p.wb) > bwd_warps) {
@@ -224,7 +224,12 @@ bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
     if (out->smem_fwd > kSmemMax || out->smem_bwd > kSmemMax) return false;
     out->n_clusters = (int)std::max<int64_t>(1, std::min<int64_t>(B, max_active_clusters_g2(out->cluster, out->smem_bwd, c->device, c->num_sm)));
     out->grid = out->n_clusters * out->cluster;
-    out->ws_cluster = align256(((size_t)out->n_clusters << (p.n + 5)) + (size_t)out->n_clusters * (1 << p.wb) * 48 * sizeof(float));
+    // L2 exchange buffers (four state-sized slices per cluster) only for programs that still have L2 exchanges,
+    // then the cross-CTA partial sums
+    bool has_l2 = false;
+    for (const MicroOp& m : p.ops) has_l2 = has_l2 || (m.kind == MOP_XCHG && m.aux == 0);
+    out->ws_cbuf = has_l2 ? ((size_t)out->n_clusters << (p.n + 5)) : 0;
+    out->ws_cluster = align256(out->ws_cbuf + (size_t)out->n_clusters * (1 << p.wb) * 48 * sizeof(float));
   } else {
     out->fwd_threads = kFwdThreads;
     size_t sf = smem_bytes(p, n_ang_in, kFwdThreads / 32, false, false);

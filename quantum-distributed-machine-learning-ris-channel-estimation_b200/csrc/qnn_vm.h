@@ -37,7 +37,8 @@ enum MopKind : int32_t {
   MOP_CU3_P = 5,      // same with control = parity(lane_in_sample & aux)
   MOP_DIAG = 6,       // multiply by diagonal table idx ([j][lane], 1024 entries); desc aux
   MOP_DIAG_REG = 7,   // diagonal that depends on register bits only (32-entry table idx); desc aux
-  MOP_XCHG = 8,       // exchange idx; aux = 1: local exchange of the cluster geometry (else through L2)
+  MOP_XCHG = 8,       // exchange idx; cluster geometry: aux = 1 local (own CTA's shared memory), aux = 2 across CTAs
+                      //   through distributed shared memory, aux = 0 through L2 buffers in the workspace
   // macro-ops: one dispatch for a whole group (the per-op dispatch latency is otherwise comparable to a body)
   MOP_ROT5 = 9,       // rotations on all five register bits; bit k uses coef row idx + pos_k and accumulator
                       //   acc + pos_k, pos_k = (aux >> 3k) & 7
@@ -77,7 +78,9 @@ struct DiagDesc {      // per DIAG / DIAG_REG micro-op
 struct Exchange {      // byte offsets into the group's buffer (8 KB per warp); address = base[thread] ^ off[j]
   uint32_t woff[32], roff[32];
   uint32_t base;       // first of 2 * G entries in Program::xbase (G = threads per group): write bases, then read bases
-  uint32_t pad[3];     // pad[0] = 1: cluster geometry, local exchange (through the CTA's own shared memory)
+  uint32_t pad[3];     // pad[0]: 0 plain / L2, 1 local exchange of the cluster geometry, 2 distributed shared memory
+                       //   (forward-direction maps; pad[1] = entry holding the backward-direction maps), 3 = such a
+                       //   backward-direction entry (pad[1] = its forward entry)
 };
 
 struct GradSlot {      // gw[weight] += accumulator[acc]  (every gradient is a direct, already-reduced sum)
@@ -120,7 +123,8 @@ std::string describe(const Program& p);   // JSON, for tests and introspection
 struct Plan {
   int threads, grid, warps_per_cta, fwd_threads;
   int cluster, n_clusters;               // CTAs per sample for n >= 14 (0: no cluster), clusters in the grid
-  size_t ws_cluster;                     // exchange buffers + cross-CTA scratch of the cluster geometry
+  size_t ws_cluster;                     // L2 exchange buffers (ws_cbuf, if the program has L2 exchanges) + cross-CTA scratch
+  size_t ws_cbuf;
   size_t smem_fwd, smem_bwd;
   size_t ws_coef, ws_diag, ws_partial;   // bytes (each 256-aligned)
 };

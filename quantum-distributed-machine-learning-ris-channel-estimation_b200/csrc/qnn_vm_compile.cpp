@@ -78,11 +78,40 @@ bool invert(const uint32_t* rowmask, int n, uint32_t* inv_col) {
   return true;
 }
 
+// Inverse of an invertible GF(2) matrix given by its columns (n <= 16).
+bool invert_cols(const uint32_t* cols, int n, uint32_t* inv) {
+  uint32_t a[16], id[16];          // rows of [M | I]
+  for (int r = 0; r < n; ++r) {
+    uint32_t row = 0;
+    for (int c = 0; c < n; ++c) if ((cols[c] >> r) & 1u) row |= 1u << c;
+    a[r] = row; id[r] = 1u << r;
+  }
+  for (int col = 0; col < n; ++col) {
+    int p = -1;
+    for (int r = col; r < n; ++r) if ((a[r] >> col) & 1u) { p = r; break; }
+    if (p < 0) return false;
+    std::swap(a[p], a[col]); std::swap(id[p], id[col]);
+    for (int r = 0; r < n; ++r) if (r != col && ((a[r] >> col) & 1u)) { a[r] ^= a[col]; id[r] ^= id[col]; }
+  }
+  for (int c = 0; c < n; ++c) {     // id rows = rows of M^-1; return its columns
+    uint32_t v = 0;
+    for (int r = 0; r < n; ++r) if ((id[r] >> c) & 1u) v |= 1u << r;
+    inv[c] = v;
+  }
+  return true;
+}
+inline uint32_t mat_vec(const uint32_t* cols, int n, uint32_t v) {
+  uint32_t r = 0;
+  for (int c = 0; c < n; ++c) if ((v >> c) & 1u) r ^= cols[c];
+  return r;
+}
+
 struct Builder {
   const qnn_circuit* c;
   Program* P;
   int n, tb;
   bool no_local = false;   // cluster geometry: never use the shared-memory (local) exchange
+  bool use_dsmem = true;   // cluster geometry: exchanges that cross CTAs go through distributed shared memory (else L2)
   int policy = 0;   // how "apply the pending diagonal" and "exchange" are ordered when both are possible
   std::vector<Item> items;
   uint32_t rowmask[16];
@@ -388,6 +417,75 @@ struct Builder {
     for (int w = 0; w < n; ++w) if (!used[w]) bit_of_wire[w] = b++;
   }
 
+  // Cluster geometry, exchange through distributed shared memory.  Every thread stores its amplitudes straight
+  // into the shared-memory buffer of the CTA that will hold them (st.shared::cluster) and, after one cluster
+  // barrier, loads its new amplitudes from its own CTA's buffer.  The slot of an amplitude is a GF(2)-linear
+  // function of its READER-side extended index: the CTA-rank bits (13..) are the reader's CTA rank, the low 13
+  // bits are R times the reader's (register, lane, warp) bits, R invertible and chosen so that
+  //   * a reading half-warp hits 16 distinct 8-byte banks, and
+  //   * where the permutation allows it, the 32 lanes of a writing warp store one contiguous 256-byte run in one
+  //     destination CTA (the images of the writer's lane bits go to slot bits 0..4).
+  // wimg[e]: reader-side extended index contributed by writer-side bit e (E bits).  Outputs as in emit_exchange:
+  // scol[writer bit], rcol[reader bit].
+  bool dsmem_maps(const uint32_t* wimg, int E, Lcg& rng, uint32_t* scol, uint32_t* rcol) {
+    const int LB = 13;
+    const uint32_t lowmask = (1u << LB) - 1u;
+    uint32_t u[5];
+    for (int i = 0; i < 5; ++i) u[i] = wimg[5 + i] & lowmask;     // low parts of the images of the writer's lane bits
+    for (int keep = 5; keep >= 0; --keep) {
+      // a maximal independent subset of the first `keep` lane images gets the contiguous-run treatment
+      int sel[5], ns = 0;
+      uint32_t chosen[13];
+      for (int i = 0; i < keep; ++i) {
+        if (!u[i]) continue;
+        chosen[ns] = u[i];
+        if (independent(chosen, ns + 1)) sel[ns++] = i;
+      }
+      for (int attempt = 0; attempt < 4000; ++attempt) {
+        uint32_t bm[13], tg[13];
+        int nb = 0;
+        for (int k = 0; k < ns; ++k) { bm[nb] = u[sel[k]]; tg[nb] = 1u << k; ++nb; }
+        int guard = 0;
+        while (nb < LB && guard++ < 1000) {                       // complete both to bases with random vectors
+          bm[nb] = rng.next() & lowmask;
+          if (!independent(bm, nb + 1)) continue;
+          int g2 = 0;
+          do { tg[nb] = rng.next() & lowmask; } while (!independent(tg, nb + 1) && g2++ < 1000);
+          if (g2 >= 1000) break;
+          ++nb;
+        }
+        if (nb < LB) continue;
+        uint32_t bminv[13], rlow[13];
+        if (!invert_cols(bm, LB, bminv)) continue;
+        for (int b = 0; b < LB; ++b) rlow[b] = mat_vec(tg, LB, bminv[b]);   // R = T * B^-1, column b
+        // reader side: lanes 0..3 of the reader (extended bits 5..8) must spread over the 16 banks of a half-warp
+        uint32_t rl[4];
+        for (int i = 0; i < 4; ++i) rl[i] = rlow[5 + i] & 15u;
+        if (!independent(rl, 4)) continue;
+        for (int b = 0; b < E; ++b) rcol[b] = b < LB ? rlow[b] : (1u << b);
+        for (int e = 0; e < E; ++e) scol[e] = mat_vec(rcol, E, wimg[e]);
+        return true;
+      }
+    }
+    return false;
+  }
+
+  void push_exchange_tables(Exchange& X, const uint32_t* scol, const uint32_t* rcol) {
+    const int G = 32 << P->wb;
+    X.base = (uint32_t)P->xbase.size();
+    for (int v = 0; v < 32; ++v) {
+      uint32_t wo = 0, ro = 0;
+      for (int i = 0; i < 5; ++i) if ((v >> i) & 1) { wo ^= scol[i]; ro ^= rcol[i]; }
+      X.woff[v] = wo * 8; X.roff[v] = ro * 8;
+    }
+    for (int side = 0; side < 2; ++side)
+      for (int t = 0; t < G; ++t) {
+        uint32_t b = 0;
+        for (int i = 0; i < 5 + P->wb; ++i) if ((t >> i) & 1) b ^= side ? rcol[5 + i] : scol[5 + i];
+        P->xbase.push_back(b * 8);
+      }
+  }
+
   bool emit_exchange(const int* new_bit_of_wire, bool allow_global = true, bool* local_out = nullptr) {
     uint32_t inv_col[16];
     if (!invert(rowmask, n, inv_col)) { P->why_not = "internal: singular layout"; return false; }
@@ -412,6 +510,29 @@ struct Builder {
       }
     if (local_out) *local_out = local;
     if (P->wb > 3 && !local && !allow_global) return true;     // caller retries with a global layout
+    if (P->wb > 3 && !local && use_dsmem) {
+      // forward direction: writers hold the old layout, readers the new one; the backward pass runs the inverse
+      // permutation and gets its own maps (entry pad[1]) so that its stores, too, are the remote side
+      uint32_t ainv[16];
+      if (!invert_cols(acol, E, ainv)) { P->why_not = "internal: singular exchange"; return false; }
+      Exchange F{}, Bk{};
+      bool ok = dsmem_maps(ainv, E, rng, scol, rcol);
+      if (ok) {
+        push_exchange_tables(F, scol, rcol);
+        ok = dsmem_maps(acol, E, rng, scol, rcol);
+        if (ok) push_exchange_tables(Bk, scol, rcol);
+      }
+      if (!ok) { P->why_not = "internal: no conflict-free distributed-shared-memory exchange found"; return false; }
+      F.pad[0] = 2u; F.pad[1] = (uint32_t)P->exchanges.size() + 1u;
+      Bk.pad[0] = 3u; Bk.pad[1] = (uint32_t)P->exchanges.size();     // 3: backward-direction tables of the entry before
+      MicroOp m{};
+      m.kind = MOP_XCHG; m.idx = (int)P->exchanges.size(); m.acc = -1; m.aux = 2;
+      P->exchanges.push_back(F);
+      P->exchanges.push_back(Bk);
+      P->ops.push_back(m);
+      for (int w = 0; w < n; ++w) rowmask[w] = 1u << new_bit_of_wire[w];
+      return true;
+    }
     const int ES = local ? 13 : E;                             // slot bits
     const uint32_t emask = (1u << ES) - 1u;
     for (int attempt = 0;; ++attempt) {
@@ -446,19 +567,7 @@ struct Builder {
       if (independent(wlow, 4) && independent(rlow, 4)) break;
     }
     Exchange X{};
-    const int G = 32 << P->wb;
-    X.base = (uint32_t)P->xbase.size();
-    for (int v = 0; v < 32; ++v) {
-      uint32_t wo = 0, ro = 0;
-      for (int i = 0; i < 5; ++i) if ((v >> i) & 1) { wo ^= scol[i]; ro ^= rcol[i]; }
-      X.woff[v] = wo * 8; X.roff[v] = ro * 8;
-    }
-    for (int side = 0; side < 2; ++side)
-      for (int t = 0; t < G; ++t) {
-        uint32_t b = 0;
-        for (int i = 0; i < 5 + P->wb; ++i) if ((t >> i) & 1) b ^= side ? rcol[5 + i] : scol[5 + i];
-        P->xbase.push_back(b * 8);
-      }
+    push_exchange_tables(X, scol, rcol);
     X.pad[0] = local ? 1u : 0u;
     MicroOp m{};
     m.kind = MOP_XCHG; m.idx = (int)P->exchanges.size(); m.acc = -1; m.aux = local ? 1 : 0;
@@ -650,7 +759,7 @@ static double program_cost(const Program& p) {
       case MOP_CU3_P: cost += 6.0; break;
       case MOP_DIAG_REG: cost += 5.0; break;
       case MOP_DIAG: cost += 6.0; break;
-      case MOP_XCHG: cost += p.wb > 3 ? (m.aux ? 8.0 : 40.0) : 4.6; break;   // cluster: shared memory vs L2
+      case MOP_XCHG: cost += p.wb > 3 ? (m.aux == 1 ? 8.0 : m.aux == 2 ? 20.0 : 40.0) : 4.6; break;   // cluster: local / DSMEM / L2
       default: break;
     }
   }
@@ -662,8 +771,9 @@ void compile(const qnn_circuit* c, Program* out) {
   // each policy and keeping the cheapest program.
   Program best;
   double best_cost = 0;
-  // Cluster geometry: local exchanges need a 64 KB buffer (plus its alignment gap) in every CTA next to the
-  // program's tables; programs whose tables leave no room for it are compiled with L2 exchanges only.
+  // Cluster geometry: shared-memory exchanges (local, and across CTAs through distributed shared memory) need two
+  // 64 KB buffers in every CTA next to the program's tables; programs whose tables leave no room for them are
+  // compiled with L2 exchanges only.
   for (int no_local = 0; no_local < 2; ++no_local) {
   if (no_local) {
     if (!best.ok || best.wb <= 3) break;
@@ -678,7 +788,7 @@ void compile(const qnn_circuit* c, Program* out) {
   for (int policy = 0; policy < 3; ++policy) {
     Program cand;
     Builder b{};
-    b.c = c; b.P = &cand; b.policy = policy; b.no_local = no_local != 0;
+    b.c = c; b.P = &cand; b.policy = policy; b.no_local = no_local != 0; b.use_dsmem = no_local == 0;
     if (!b.run()) {
       cand.ok = false;
       cand.ops.clear();
@@ -744,7 +854,7 @@ std::string describe(const Program& p) {
     tab("woff", X.woff, 32, false);
     tab("rbase", p.xbase.data() + X.base + G, G, false);
     tab("roff", X.roff, 32, false);
-    o << ", \"local\": " << X.pad[0] << "}";
+    o << ", \"local\": " << X.pad[0] << ", \"link\": " << X.pad[1] << "}";
   }
   o << "], \"slots\": [";
   for (size_t i = 0; i < p.slots.size(); ++i) {

@@ -305,28 +305,59 @@ __device__ __forceinline__ float warp_sum4(float t0, float t1, float t2, float t
 // ---- exchange ---------------------------------------------------------------------------------------
 // wa / ra: this thread's write / read base (buffer address | per-thread offset); `sync` is the barrier
 // of the group that shares the buffer (a warp for n <= 10, 2^wb warps above).
-template <typename Sync>
-__device__ __forceinline__ void exchange(float2 (&st)[NA], uint32_t wa, uint32_t ra, const uint32_t* woff,
-                                         const uint32_t* roff, Sync sync) {
-  sync();
+// buf: 0 when wa / ra already carry the (size-aligned) buffer address; else the buffer's shared address, added
+// after the XOR (cluster geometry: its two 64 KB buffers are not aligned to their size).
+__device__ __forceinline__ void smem_store_all(const float2 (&st)[NA], uint32_t buf, uint32_t wa, const uint32_t* woff) {
 #pragma unroll
   for (int q = 0; q < NA / 4; ++q) {
     const uint4 o = *reinterpret_cast<const uint4*>(woff + 4 * q);
-    sts64(wa ^ o.x, st[4 * q + 0].x, st[4 * q + 0].y);
-    sts64(wa ^ o.y, st[4 * q + 1].x, st[4 * q + 1].y);
-    sts64(wa ^ o.z, st[4 * q + 2].x, st[4 * q + 2].y);
-    sts64(wa ^ o.w, st[4 * q + 3].x, st[4 * q + 3].y);
+    sts64(buf + (wa ^ o.x), st[4 * q + 0].x, st[4 * q + 0].y);
+    sts64(buf + (wa ^ o.y), st[4 * q + 1].x, st[4 * q + 1].y);
+    sts64(buf + (wa ^ o.z), st[4 * q + 2].x, st[4 * q + 2].y);
+    sts64(buf + (wa ^ o.w), st[4 * q + 3].x, st[4 * q + 3].y);
   }
-  sync();
+}
+__device__ __forceinline__ void smem_load_all(float2 (&st)[NA], uint32_t buf, uint32_t ra, const uint32_t* roff) {
 #pragma unroll
   for (int q = 0; q < NA / 4; ++q) {
     const uint4 o = *reinterpret_cast<const uint4*>(roff + 4 * q);
-    lds64(ra ^ o.x, st[4 * q + 0].x, st[4 * q + 0].y);
-    lds64(ra ^ o.y, st[4 * q + 1].x, st[4 * q + 1].y);
-    lds64(ra ^ o.z, st[4 * q + 2].x, st[4 * q + 2].y);
-    lds64(ra ^ o.w, st[4 * q + 3].x, st[4 * q + 3].y);
+    lds64(buf + (ra ^ o.x), st[4 * q + 0].x, st[4 * q + 0].y);
+    lds64(buf + (ra ^ o.y), st[4 * q + 1].x, st[4 * q + 1].y);
+    lds64(buf + (ra ^ o.z), st[4 * q + 2].x, st[4 * q + 2].y);
+    lds64(buf + (ra ^ o.w), st[4 * q + 3].x, st[4 * q + 3].y);
   }
 }
+template <typename Sync>
+__device__ __forceinline__ void exchange(float2 (&st)[NA], uint32_t buf, uint32_t wa, uint32_t ra, const uint32_t* woff,
+                                         const uint32_t* roff, Sync sync) {
+  sync();
+  smem_store_all(st, buf, wa, woff);
+  sync();
+  smem_load_all(st, buf, ra, roff);
+}
+
+// Cluster geometry, exchange across CTAs through distributed shared memory: every amplitude is stored straight
+// into the buffer of the CTA that will hold it.  A slot's byte offset carries the destination CTA's rank in bits
+// 16.. and the offset inside that CTA's 64 KB buffer below; `buf` is the buffer's shared address (the same in
+// every CTA of the cluster).  TMA is not involved: these are plain st.shared::cluster stores.
+__device__ __forceinline__ void st_cluster64(uint32_t local_addr, uint32_t rank, float a, float b) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(rank));
+  asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(remote), "f"(a), "f"(b) : "memory");
+}
+__device__ __forceinline__ void dsmem_store_all(const float2 (&st)[NA], uint32_t buf, uint32_t wa, const uint32_t* woff) {
+#pragma unroll
+  for (int q = 0; q < NA / 4; ++q) {
+    const uint4 o = *reinterpret_cast<const uint4*>(woff + 4 * q);
+    uint32_t s;
+    s = wa ^ o.x; st_cluster64(buf + (s & 0xFFFFu), s >> 16, st[4 * q + 0].x, st[4 * q + 0].y);
+    s = wa ^ o.y; st_cluster64(buf + (s & 0xFFFFu), s >> 16, st[4 * q + 1].x, st[4 * q + 1].y);
+    s = wa ^ o.z; st_cluster64(buf + (s & 0xFFFFu), s >> 16, st[4 * q + 2].x, st[4 * q + 2].y);
+    s = wa ^ o.w; st_cluster64(buf + (s & 0xFFFFu), s >> 16, st[4 * q + 3].x, st[4 * q + 3].y);
+  }
+}
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 
 // Cluster geometry (n >= 14): the buffers are slices of the workspace (L2), accessed around L1.  Buffer
 // sets alternate from one exchange to the next, so ONE cluster barrier per exchange suffices: a set is
@@ -449,8 +480,10 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
   Smem S;
   {
     const uint32_t s0 = (uint32_t)__cvta_generic_to_shared(smem_raw);
-    const uint32_t gbuf = CL ? 65536u : (8192u << wbits);   // cluster: one CTA-wide buffer for the local exchanges
-    const uint32_t xb = (s0 + a.table_bytes + gbuf - 1u) & ~(gbuf - 1u);
+    // cluster geometry: two CTA-wide 64 KB buffers right behind the tables (addressed as base + offset, so they
+    // need no alignment to their size); otherwise one buffer per group at the next multiple of its size
+    const uint32_t gbuf = CL ? 65536u : (8192u << wbits);
+    const uint32_t xb = CL ? ((s0 + a.table_bytes + 15u) & ~15u) : ((s0 + a.table_bytes + gbuf - 1u) & ~(gbuf - 1u));
     S.xbuf = xb + (uint32_t)grp * gbuf;
     unsigned char* const p = smem_raw;
     // table offsets come from the host (constant bank): the pointers are then cheap to rematerialise
@@ -508,7 +541,7 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
   // cluster geometry: four exchange buffers per cluster (two alternating sets of {psi, lam})
   unsigned char* const cbuf = CL ? a.cbuf + ((size_t)cid << (a.n + 5)) : nullptr;
   const size_t cbuf_one = (size_t)1 << (a.n + 3);
-  unsigned xpar = 0;
+  unsigned xpar = 0, xl2 = 0;   // buffer parities: shared-memory pair (forward program), L2 pair
   float* const cred = CL ? a.cred + (size_t)cid * gwarps * 48 : nullptr;
 
   float2* const xcoef = S.xcoef + (size_t)warp * spw * max(a.n_angle, 1);
@@ -619,20 +652,31 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
           case H_XCHG: {
             const Exchange* X = S.exchanges + op.idx;
             if constexpr (CL) {
-              if (op.aux) {   // local: the CTA bits stay put, the exchange runs through this CTA's shared memory
-                exchange(ps, S.xbuf | S.xbase[X->base + tig], S.xbuf | S.xbase[X->base + G + tig], X->woff, X->roff, csync);
-              } else {
+              if (op.aux == 1) {   // local: the CTA bits stay put, the exchange runs through this CTA's shared memory
+                exchange(ps, S.xbuf + (xpar << 16), S.xbase[X->base + tig], S.xbase[X->base + G + tig], X->woff, X->roff, csync);
+              } else if (op.aux == 2) {
+                // Across CTAs through distributed shared memory.  The two buffers alternate from one such exchange
+                // to the next and the local exchanges in between use the one received into last, so ONE cluster
+                // barrier per exchange suffices: a buffer is written remotely only by CTAs that have passed the
+                // barrier of the exchange in between, which this CTA reaches after its last use of that buffer.
                 xpar ^= 1u;
-                unsigned char* b0 = cbuf + (size_t)(2 * xpar) * cbuf_one;
+                const uint32_t buf = S.xbuf + (xpar << 16);
+                dsmem_store_all(ps, buf, S.xbase[X->base + tig], X->woff);
+                gsync();
+                smem_load_all(ps, buf, S.xbase[X->base + G + tig] & 0xFFFFu, X->roff);
+              } else {
+                xl2 ^= 1u;
+                unsigned char* b0 = cbuf + (size_t)(2 * xl2) * cbuf_one;
                 exchange_global<false>(ps, ps, b0, b0, S.xbase[X->base + tig], S.xbase[X->base + G + tig], X->woff, X->roff, gsync);
               }
-            } else exchange(ps, S.xbuf | S.xbase[X->base + tig], S.xbuf | S.xbase[X->base + G + tig], X->woff, X->roff, gsync);
+            } else exchange(ps, 0u, S.xbuf | S.xbase[X->base + tig], S.xbuf | S.xbase[X->base + G + tig], X->woff, X->roff, gsync);
           } break;
           default: break;
         }
         op = next;
       }
     }
+    if constexpr (CL && BWD && !STATE) { gsync(); xpar = 0; }   // the reverse sweep starts with both shared buffers free
     }  // forward program (skipped when the backward pass starts from a saved state)
 
     if constexpr (!BWD && STATE) {
@@ -814,19 +858,36 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
           case H_XCHG: {   // inverse: roles of the two address sets swapped
             const Exchange* X = S.exchanges + op.idx;
             if constexpr (CL) {
-              const uint32_t wa = S.xbase[X->base + G + tig], ra = S.xbase[X->base + tig];
-              if (op.aux) {
-                exchange(ps, S.xbuf | wa, S.xbuf | ra, X->roff, X->woff, csync);
-                exchange(ls, S.xbuf | wa, S.xbuf | ra, X->roff, X->woff, csync);
+              if (op.aux == 2) {
+                // The inverse permutation has its own maps (entry pad[1]) so that here, too, stores are the remote
+                // side and loads stay in this CTA.  psi travels through buffer 0 and lam through buffer 1, each
+                // behind its own cluster barrier; the local exchanges of the reverse sweep use buffer 1 only.  So
+                // buffer 0 is written remotely after the lam barrier of the previous exchange (this CTA's psi loads
+                // from it precede that barrier) and buffer 1 after this exchange's psi barrier (which this CTA
+                // reaches after its local exchanges).  The lam stores overlap with the psi loads.
+                const Exchange* Xb = S.exchanges + X->pad[1];
+                const uint32_t wa = S.xbase[Xb->base + tig], ra = S.xbase[Xb->base + G + tig] & 0xFFFFu;
+                dsmem_store_all(ps, S.xbuf, wa, Xb->woff);
+                cluster_arrive(); cluster_wait();
+                dsmem_store_all(ls, S.xbuf + 65536u, wa, Xb->woff);
+                smem_load_all(ps, S.xbuf, ra, Xb->roff);
+                cluster_arrive(); cluster_wait();
+                smem_load_all(ls, S.xbuf + 65536u, ra, Xb->roff);
               } else {
-                xpar ^= 1u;
-                unsigned char* b0 = cbuf + (size_t)(2 * xpar) * cbuf_one;
-                exchange_global<true>(ps, ls, b0, b0 + cbuf_one, wa, ra, X->roff, X->woff, gsync);
+                const uint32_t wa = S.xbase[X->base + G + tig], ra = S.xbase[X->base + tig];
+                if (op.aux == 1) {
+                  exchange(ps, S.xbuf + 65536u, wa, ra, X->roff, X->woff, csync);
+                  exchange(ls, S.xbuf + 65536u, wa, ra, X->roff, X->woff, csync);
+                } else {
+                  xl2 ^= 1u;
+                  unsigned char* b0 = cbuf + (size_t)(2 * xl2) * cbuf_one;
+                  exchange_global<true>(ps, ls, b0, b0 + cbuf_one, wa, ra, X->roff, X->woff, gsync);
+                }
               }
             } else {
               const uint32_t wa = S.xbuf | S.xbase[X->base + G + tig], ra = S.xbuf | S.xbase[X->base + tig];
-              exchange(ps, wa, ra, X->roff, X->woff, gsync);
-              exchange(ls, wa, ra, X->roff, X->woff, gsync);
+              exchange(ps, 0u, wa, ra, X->roff, X->woff, gsync);
+              exchange(ls, 0u, wa, ra, X->roff, X->woff, gsync);
             }
           } break;
           default: break;

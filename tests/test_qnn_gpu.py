@@ -126,7 +126,7 @@ def test_deep_cluster_circuit_falls_back_to_l2_exchanges():
     assert _plan(c, 2) == "vm-register"
     check_against_oracle(c, 2, seed=7)
     # just below the switch: local exchanges are used and the program still fits
-    c16 = qris_b200.u3cu3_circuit(14, 16)
+    c16 = qris_b200.u3cu3_circuit(14, 12)
     assert sum(x["local"] for x in c16.describe()["exchanges"]) > 0 and _plan(c16, 2) == "vm-register"
 
 

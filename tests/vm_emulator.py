@@ -56,6 +56,37 @@ def check_conflict_free(base, off, writing=True, local=False):
             assert len(slots) == 16, "shared-memory bank conflict in an exchange"
 
 
+def dsmem_exchange(state, X, G, stats):
+    """Exchange across the CTAs of a cluster through distributed shared memory: a slot's byte offset holds the
+    destination CTA's rank in bits 16.. and the offset in that CTA's 64 KB buffer below.  Every thread must READ
+    only its own CTA's buffer, without bank conflicts; a writing warp's 32 stores should fill eight whole 32-byte sectors
+    (one 256-byte run, or a few runs in different CTAs when a lane bit's wire moves to a CTA-rank bit): counted."""
+    n_cta = G // 256
+    buf = {}
+    runs = 0
+    for jj in range(32):
+        for w0 in range(0, G, 32):
+            addrs = [X["wbase"][l] ^ X["woff"][jj] for l in range(w0, w0 + 32)]
+            runs += len({a // 32 for a in addrs}) == 8      # eight full 32-byte sectors: nothing wasted
+            for l, addr in zip(range(w0, w0 + 32), addrs):
+                assert addr % 8 == 0 and 0 <= (addr >> 16) < n_cta and addr not in buf
+                buf[addr] = state[l, jj]
+    new = np.empty_like(state)
+    for l in range(G):
+        for jj in range(32):
+            addr = X["rbase"][l] ^ X["roff"][jj]
+            assert addr >> 16 == l // 256, "a thread reads another CTA's buffer"
+            new[l, jj] = buf[addr]
+    for jj in range(32):
+        for half in range(0, G, 16):
+            slots = {(((X["rbase"][l] ^ X["roff"][jj]) & 0xFFFF) // 8) % 16 for l in range(half, half + 16)}
+            assert len(slots) == 16, "shared-memory bank conflict on the reading side of a DSMEM exchange"
+    if stats is not None:
+        stats["dsmem_sector_exact_warp_stores"] = stats.get("dsmem_sector_exact_warp_stores", 0) + runs
+        stats["dsmem_warp_stores"] = stats.get("dsmem_warp_stores", 0) + 32 * (G // 32)
+    return new
+
+
 def emulate_forward(desc, x, w):
     """x: (samples_per_warp, n_inputs); returns y (samples_per_warp, n)."""
     assert desc["ok"]
@@ -149,8 +180,19 @@ def emulate_forward(desc, x, w):
             stats["diag" if kind == MOP_DIAG else "diag_reg"] += 1
         elif kind == MOP_XCHG:
             X = desc["exchanges"][idx]
-            local = bool(X.get("local", 0))          # cluster geometry: through each CTA's own 64 KB buffer
-            assert local == bool(aux) and (not local or G > 256)
+            mode = int(X.get("local", 0))   # cluster geometry: 1 own CTA's buffer, 2 distributed shared memory, 0 L2 / plain
+            assert mode == aux and (mode == 0 or G > 256)
+            if mode == 2:
+                new = dsmem_exchange(state, X, G, stats)
+                # the backward pass runs the inverse permutation with the maps of the linked entry
+                Xb = desc["exchanges"][X["link"]]
+                assert Xb["local"] == 3 and Xb["link"] == idx
+                back = dsmem_exchange(new, Xb, G, None)
+                assert np.array_equal(back, state), "backward-direction maps do not invert the exchange"
+                state = new
+                stats["xchg"] += 1
+                continue
+            local = mode == 1
             check_conflict_free(X["wbase"], X["woff"], local=local)
             check_conflict_free(X["rbase"], X["roff"], writing=False, local=local)
             size = 65536 if local else 8192 * (G // 32)
