@@ -60,7 +60,8 @@ def test_request_beyond_the_array_is_refused():
     circ = qris_b200.u3cu3_circuit(15, 1)          # 64 samples in flight: 32 MiB of state vectors
     h = circ.handle(0)
     B = 64
-    assert lib.qnn_backward_workspace_bytes(h, B) > lib.qnn_static_scratch_bytes()
+    # the static entry point runs the generic kernel family: its scratch need is that family's workspace
+    assert lib.qnn_backward_workspace_bytes(circ.generic().handle(0), B) > lib.qnn_static_scratch_bytes()
     x = torch.zeros(B, 15, device="cuda"); w = torch.zeros(circ.n_weights, device="cuda")
     gy = torch.zeros(B, 15, device="cuda"); gx = torch.empty_like(x); gw = torch.empty_like(w)
     rc = lib.qnn_backward_static(h, x.data_ptr(), w.data_ptr(), gy.data_ptr(), gx.data_ptr(), gw.data_ptr(), B, None)
