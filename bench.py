@@ -12,7 +12,10 @@ reference's n=6, L=3 circuit at batch 4096) -- launch-bound by construction (SUR
 One step = weight noise -> qnn_forward -> QuantumNAT forward -> QuantumNAT backward -> qnn_backward
 (adjoint VJP: gx and batch-reduced gw) [-> one NCCL all-reduce of gw when N > 1], on inputs resident in
 HBM (`value`); `e2e` is the same work driven through the nn.Module surface with pinned-host inputs
-copied in and the loss read back every step.  Prints ONE JSON line (rank 0).
+copied in and the loss read back every step.  Prints ONE JSON line (rank 0).  The device-timed step (and the
+forward / backward calls timed alone for the roofline block) is recorded once as a CUDA graph and replayed, so that
+small workloads measure the kernels and not the host's per-call cost (`--eager` launches every step from Python
+instead; the all-reduce of a multi-GPU step always stays outside the recording; the e2e step is always eager).
 
 Besides the headline workload the line carries a ``secondary`` list of short device-timed records, each with
 its own roofline block, so that every number quoted in README/DESIGN comes out of a driver run: ``cfg4``
@@ -269,6 +272,7 @@ class Ctx:
             os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
             dist.init_process_group("nccl", device_id=self.dev)
         self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)     # > 126 MB L2
+        self.eager = False
 
     def barrier(self):
         if self.world > 1:
@@ -280,6 +284,29 @@ class Ctx:
         if self.world > 1:
             self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
         return t.item()
+
+
+def record_graph(torch, fn):
+    """Record `fn` (kernel launches on static tensors) once into a CUDA graph and return its replay; the eager
+    function itself if recording is not possible.  Launch-bound steps (small batches: a few kernels of tens of
+    microseconds) are then bound by the device, not by the host's per-call cost."""
+    try:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                fn()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=side):
+            fn()
+        g.replay()
+        torch.cuda.synchronize()
+        return g.replay, "recorded once as a CUDA graph and replayed"
+    except Exception as e:                                     # keep measuring, and say so in the record
+        torch.cuda.synchronize()
+        return fn, f"eager (graph recording failed: {type(e).__name__})"
 
 
 def measure_workload(ctx, wl, B, steps, warmup, clocks=None):
@@ -301,22 +328,27 @@ def measure_workload(ctx, wl, B, steps, warmup, clocks=None):
     h = circ.handle(ctx.local_rank)
     launches_per_step = lib.qnn_forward_launches(h, B) + lib.qnn_backward_launches(h, B) + (6 if qnat else 0)
 
+    def compute():
+        wn = w + 0.01 * torch.randn_like(w) if qnat else w           # weight-space noise (Est:186-188)
+        y, state = qris_b200.qnn_forward_raw(circ, x, wn, save_state=True)   # keeps psi_final for the adjoint pass
+        if qnat:
+            yq = y.detach().requires_grad_(True)
+            out = head(yq)
+            out.backward(gout)
+            gy = yq.grad
+        else:
+            gy = gout
+        gx, _ = qris_b200.qnn_backward_raw(circ, x, wn, gy, need_gx=True, gw_out=gw_bucket, state=state)
+        return gx
+
+    replay, launch_mode = record_graph(torch, compute) if not ctx.eager else (compute, "eager (--eager)")
+
     def step():
         with torch.cuda.nvtx.range("bench/step"):
-            wn = w + 0.01 * torch.randn_like(w) if qnat else w           # weight-space noise (Est:186-188)
-            y, state = qris_b200.qnn_forward_raw(circ, x, wn, save_state=True)   # keeps psi_final for the adjoint pass
-            if qnat:
-                yq = y.detach().requires_grad_(True)
-                out = head(yq)
-                out.backward(gout)
-                gy = yq.grad
-            else:
-                gy = gout
-            gx, _ = qris_b200.qnn_backward_raw(circ, x, wn, gy, need_gx=True, gw_out=gw_bucket, state=state)
-            if ctx.world > 1:
+            replay()
+            if ctx.world > 1:                                    # the collective stays outside the recording
                 with torch.cuda.nvtx.range("allreduce/gw"):
                     dist.all_reduce(gw_bucket)
-        return gx
 
     for _ in range(max(warmup, 3)):
         step()
@@ -335,13 +367,22 @@ def measure_workload(ctx, wl, B, steps, warmup, clocks=None):
     ms_per_step = total_ms / steps
     # dominant kernel (adjoint backward) and the forward kernel, timed alone on the same stream
     gy_fixed = torch.randn(B, n, device=dev)
+    keep = {}
+
+    def fwd_only():
+        keep["state"] = qris_b200.qnn_forward_raw(circ, x, w, save_state=True)[1]
+
+    def bwd_only():
+        qris_b200.qnn_backward_raw(circ, x, w, gy_fixed, need_gx=True, gw_out=gw_bucket, state=keep["state"])
+    fwd_replay = record_graph(torch, fwd_only)[0] if not ctx.eager else fwd_only
+    bwd_replay = record_graph(torch, bwd_only)[0] if not ctx.eager else bwd_only
     k_bwd, k_fwd = [], []
     for _ in range(max(5, min(steps, 20))):
         ctx.flush.zero_()
         s1, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s2, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s2.record(); _, st_k = qris_b200.qnn_forward_raw(circ, x, w, save_state=True); e2.record()
-        s1.record(); qris_b200.qnn_backward_raw(circ, x, w, gy_fixed, need_gx=True, gw_out=gw_bucket, state=st_k); e1.record()
+        s2.record(); fwd_replay(); e2.record()
+        s1.record(); bwd_replay(); e1.record()
         torch.cuda.synchronize()
         k_bwd.append(s1.elapsed_time(e1)); k_fwd.append(s2.elapsed_time(e2))
     bwd_ms, fwd_ms = statistics.mean(k_bwd), statistics.mean(k_fwd)
@@ -362,16 +403,66 @@ def measure_workload(ctx, wl, B, steps, warmup, clocks=None):
         "saved_state_bytes_per_outstanding_forward": int(lib.qnn_state_bytes(h, B)),
     }
     return {"circ": circ, "value": B * ctx.world / (ms_per_step * 1e-3), "ms_per_step": ms_per_step, "roofline": roofline,
-            "launches_per_step": launches_per_step, "head": head, "desc": desc, "n": n, "L": L,
+            "launches_per_step": launches_per_step, "head": head, "desc": desc, "n": n, "L": L, "launch": launch_mode,
             "plan": lib.qnn_circuit_plan(h, B).decode()}
 
 
-def secondary_record(ctx, wl, B, steps, scaling, name=None):
+def measure_e2e(ctx, m, B, qnat, steps, warmup):
+    """The same metric end to end through the module surface (the call a user makes): every step copies its inputs
+    from pinned host memory, runs QNNLayer (+ QuantumNAT head) + a linear classifier + loss forward and backward
+    into the flat gradient bucket, all-reduces it, and reads the loss back."""
+    import torch.nn.functional as F
+
+    import qris_b200
+    from qris_b200.parallel import FlatGradBucket
+    torch, dev, n = ctx.torch, ctx.dev, m["n"]
+    circ, head = m["circ"], m["head"]
+    torch.manual_seed(5)
+    layer = qris_b200.QNNLayer(circ).to(dev)
+    clf = torch.nn.Linear(n, 3).to(dev)
+    params = list(layer.parameters()) + list(clf.parameters())
+    bucket = FlatGradBucket(params)
+    xh = (2 * torch.rand(B, n) - 1).pin_memory()
+    lh = torch.randint(0, 3, (B,)).pin_memory()
+
+    def e2e_step():
+        bucket.zero()
+        xd = xh.to(dev, non_blocking=True).requires_grad_(True)
+        ld = lh.to(dev, non_blocking=True)
+        if qnat:                                                      # Est:176-196 on the layer's own weights
+            with torch.no_grad():
+                saved = layer.weights.data.clone()
+                layer.weights.data.add_(0.01 * torch.randn_like(layer.weights))
+        y = layer(xd)
+        if qnat:
+            with torch.no_grad():
+                layer.weights.data.copy_(saved)
+            y = head(y)
+        loss = F.nll_loss(F.log_softmax(clf(y), dim=1), ld)
+        loss.backward()
+        bucket.all_reduce()
+        return loss.item()                                            # device -> host read every step
+
+    for _ in range(max(warmup, 3)):
+        e2e_step()
+    ctx.barrier()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for s_, e_ in ev:
+        ctx.flush.zero_()
+        s_.record(); e2e_step(); e_.record()
+    ctx.barrier()
+    e2e_ms = ctx.max_over_ranks(sum(s_.elapsed_time(e_) for s_, e_ in ev))
+    return {"value": B * ctx.world / (e2e_ms / steps * 1e-3), "unit": "samples/s",
+            "h2d_bytes_per_step": xh.numel() * 4 + lh.numel() * 8, "d2h_bytes_per_step": 4}
+
+
+def secondary_record(ctx, wl, B, steps, scaling, name=None, with_e2e=False):
     m = measure_workload(ctx, wl, B, steps, 3)
     r = m["roofline"]
-    return {"name": name or wl, "workload": m["desc"], "metric": "qnn_samples_per_sec_fwd_bwd", "value": m["value"],
+    extra = {"e2e": measure_e2e(ctx, m, B, WORKLOADS[wl][4], steps, 3)} if with_e2e else {}
+    return {**extra, "name": name or wl, "workload": m["desc"], "metric": "qnn_samples_per_sec_fwd_bwd", "value": m["value"],
             "unit": "samples/s", "n_gpus": ctx.world, "steps": steps, "ms_per_step": m["ms_per_step"], "scaling": scaling,
-            "batch_per_gpu": B, "global_batch": B * ctx.world, "plan": m["plan"],
+            "batch_per_gpu": B, "global_batch": B * ctx.world, "plan": m["plan"], "launch": m["launch"],
             "roofline": {k: r[k] for k in ("bound", "achieved", "peak", "unit", "frac", "step_frac", "step_achieved", "kernel_ms",
                                            "algorithmic_flops_per_sample", "traffic", "traffic_source")}}
 
@@ -425,6 +516,7 @@ def run_b200(args, wl):
     from qris_b200.parallel import FlatGradBucket
 
     ctx = Ctx()
+    ctx.eager = bool(args.eager)
     dist, dev, world, rank = ctx.dist, ctx.dev, ctx.world, ctx.rank
     kind, n, L, B, qnat, desc = WORKLOADS[wl]
     if args.batch:
@@ -436,44 +528,8 @@ def run_b200(args, wl):
     launches_per_step = m["launches_per_step"]
     flush, barrier = ctx.flush, ctx.barrier
 
-    # ---- end to end through the module surface: pinned host -> device, loss read back ----
-    torch.manual_seed(5)
-    layer = qris_b200.QNNLayer(circ).to(dev)
-    clf = torch.nn.Linear(n, 3).to(dev)
-    params = list(layer.parameters()) + list(clf.parameters())
-    bucket = FlatGradBucket(params)
-    xh = (2 * torch.rand(B, n) - 1).pin_memory()
-    lh = torch.randint(0, 3, (B,)).pin_memory()
-    e2e_launches = launches_per_step
-
-    def e2e_step():
-        bucket.zero()
-        xd = xh.to(dev, non_blocking=True).requires_grad_(True)
-        ld = lh.to(dev, non_blocking=True)
-        if qnat:                                                      # Est:176-196 on the layer's own weights
-            with torch.no_grad():
-                saved = layer.weights.data.clone()
-                layer.weights.data.add_(0.01 * torch.randn_like(layer.weights))
-        y = layer(xd)
-        if qnat:
-            with torch.no_grad():
-                layer.weights.data.copy_(saved)
-            y = head(y)
-        loss = F.nll_loss(F.log_softmax(clf(y), dim=1), ld)
-        loss.backward()
-        bucket.all_reduce()
-        return loss.item()                                            # device -> host read every step
-
-    for _ in range(max(args.warmup, 3)):
-        e2e_step()
-    barrier()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    for s, e in ev:
-        flush.zero_()
-        s.record(); e2e_step(); e.record()
-    barrier()
-    e2e_ms = ctx.max_over_ranks(sum(s.elapsed_time(e) for s, e in ev))
-    e2e_value = B * world / (e2e_ms / args.steps * 1e-3)
+    e2e = measure_e2e(ctx, m, B, qnat, args.steps, args.warmup)
+    e2e_value = e2e["value"]
 
     # ---- secondary records: every other number the documentation quotes (all ranks take part) ----
     secondary = []
@@ -482,7 +538,7 @@ def run_b200(args, wl):
             secondary.append(secondary_record(ctx, "cfg3", WORKLOADS["cfg3"][3] // world, max(5, min(args.steps, 20)), "strong",
                                               name="cfg3_strong"))
         secondary.append(secondary_record(ctx, "cfg4", WORKLOADS["cfg4"][3], 5, "weak"))
-        secondary.append(secondary_record(ctx, "cfg2", WORKLOADS["cfg2"][3], max(5, min(args.steps, 20)), "weak"))
+        secondary.append(secondary_record(ctx, "cfg2", WORKLOADS["cfg2"][3], max(5, min(args.steps, 20)), "weak", with_e2e=True))
         if world == 1:
             secondary.append(cfg1_record(ctx))
 
@@ -507,11 +563,10 @@ def run_b200(args, wl):
             "config": {"workload": desc, "name": wl, "n_qubits": n, "n_layers": L, "batch_per_gpu": B,
                        "global_batch": B * world, "parallelism": f"dp{world}",
                        "l2": "flushed between timed steps (256 MiB memset, outside the per-step CUDA events)",
-                       "plan": m["plan"]},
+                       "plan": m["plan"], "launch": "device-timed step " + m["launch"] + "; e2e step eager"},
             "clocks": clocks.summary(),
-            "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": xh.numel() * 4 + lh.numel() * 8,
-                    "d2h_bytes_per_step": 4},
-            "gpu_launches": launches_per_step * args.steps + e2e_launches * args.steps,
+            "e2e": e2e,
+            "gpu_launches": 2 * launches_per_step * args.steps,
             "roofline": roofline,
             "secondary": secondary,
         }
@@ -541,6 +596,7 @@ def main():
     ap.add_argument("--workload", default="cfg3", choices=sorted(WORKLOADS))
     ap.add_argument("--batch", type=int, default=0, help="override the per-GPU batch")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--eager", action="store_true", help="launch every device-timed step eagerly instead of replaying a CUDA graph")
     ap.add_argument("--no-secondary", action="store_true", help="skip the secondary records (cfg4, cfg2, cfg1, strong scaling)")
     args = ap.parse_args()
     # The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version line at the

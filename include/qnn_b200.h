@@ -80,6 +80,14 @@ QNN_API int qnn_circuit_create(const qnn_op* ops, int32_t n_ops, int32_t n_qubit
  * interpreter) kernel family even where the register-resident family applies; the parity tests use it to
  * check one family against the other.  No counterpart in the reference. */
 #define QNN_CREATE_GENERIC_ONLY 1u
+/* Kernel-variant pins for measurements and tests.  By default a circuit of up to 8 qubits is lowered twice: to the wide
+ * variant (32 amplitudes per thread, a warp carries 1024: the throughput geometry) and to the narrow one (8 per thread,
+ * a warp carries 256), and each call picks by its batch size -- the reference's own sizes (256 to 4,096 samples of a
+ * 6-qubit circuit, Run:341-352) would occupy 1 to 16 CTAs of the wide variant.  WIDE_ONLY / NARROW_ONLY pin one of them;
+ * 16_PER_THREAD lowers the circuit (n <= 12) with 16 amplitudes per thread instead (an occupancy experiment). */
+#define QNN_CREATE_WIDE_ONLY 2u
+#define QNN_CREATE_NARROW_ONLY 4u
+#define QNN_CREATE_16_PER_THREAD 8u
 QNN_API int qnn_circuit_create_ex(const qnn_op* ops, int32_t n_ops, int32_t n_qubits, int32_t n_inputs,
                                   int32_t n_weights, int32_t encoder, uint32_t flags, qnn_circuit** out);
 QNN_API void qnn_circuit_destroy(qnn_circuit* c);

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """ncu driver: saved-state forward + two saved-state backward calls of the U3+CU3 circuit at n qubits.
 
-    python profiles/experiments/prof_n.py n [L] [B]
+    python profiles/experiments/prof_n.py n [L] [B] [variant: wide | narrow | 16-per-thread]
 """
 import os
 import sys
@@ -15,6 +15,8 @@ import qris_b200  # noqa: E402
 n = int(sys.argv[1]); L = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 B = int(sys.argv[3]) if len(sys.argv) > 3 else max(148, (1 << 23) >> n)
 circ = qris_b200.u3cu3_circuit(n, L)
+if len(sys.argv) > 4:
+    circ = circ.pinned(sys.argv[4])
 torch.manual_seed(0)
 x = (2 * torch.rand(B, n, device="cuda") - 1)
 w = 2 * torch.pi * torch.rand(circ.n_weights, device="cuda")

@@ -16,7 +16,10 @@ SRC_CONST = -(2 ** 31)
 GATE = {"RX": 0, "RY": 1, "RZ": 2, "U3": 3, "CNOT": 4, "CZ": 5, "CU3": 6}
 GATE_ANGLES = {"RX": 1, "RY": 1, "RZ": 1, "U3": 3, "CNOT": 0, "CZ": 0, "CU3": 3}
 ENCODER = {"none": 0, "amplitude": 1}
-CREATE_GENERIC_ONLY = 1   # qnn_circuit_create_ex flag
+# qnn_circuit_create_ex flags (include/qnn_b200.h)
+CREATE_GENERIC_ONLY, CREATE_WIDE_ONLY, CREATE_NARROW_ONLY, CREATE_16_PER_THREAD = 1, 2, 4, 8
+VARIANT_FLAGS = {None: 0, "generic": CREATE_GENERIC_ONLY, "wide": CREATE_WIDE_ONLY, "narrow": CREATE_NARROW_ONLY,
+                 "16-per-thread": CREATE_16_PER_THREAD}
 
 
 class QnnOp(C.Structure):

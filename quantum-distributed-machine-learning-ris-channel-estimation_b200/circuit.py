@@ -28,7 +28,7 @@ class Circuit:
     """Immutable gate list + lazily created device handles (one per CUDA device)."""
 
     def __init__(self, n_qubits: int, ops: Sequence[Op], n_inputs: int, n_weights: int,
-                 encoder: str = "none", generic_only: bool = False):
+                 encoder: str = "none", generic_only: bool = False, variant: str = None):
         if encoder not in _lib.ENCODER:
             raise ValueError(f"encoder must be one of {sorted(_lib.ENCODER)}, got {encoder!r}")
         self.n_qubits = int(n_qubits)
@@ -38,6 +38,11 @@ class Circuit:
         # keep the circuit on the generic kernel family (QNN_CREATE_GENERIC_ONLY): the parity tests use it to
         # check one kernel family against the other
         self.generic_only = bool(generic_only)
+        # pin one kernel variant ("generic", "wide", "narrow", "16-per-thread": QNN_CREATE_* flags) for tests and
+        # measurements; None lets every call choose by its batch size
+        self.variant = "generic" if generic_only else variant
+        if self.variant not in _lib.VARIANT_FLAGS:
+            raise ValueError(f"variant must be one of {sorted(k for k in _lib.VARIANT_FLAGS if k)}, got {variant!r}")
         self.ops: Tuple[Op, ...] = tuple(ops)
         for op in self.ops:
             if op.kind not in _lib.GATE:
@@ -69,13 +74,17 @@ class Circuit:
         return arr
 
     def _create(self, out):
-        flags = _lib.CREATE_GENERIC_ONLY if self.generic_only else 0
+        flags = _lib.VARIANT_FLAGS[self.variant]
         return _lib.lib().qnn_circuit_create_ex(self.c_ops(), len(self.ops), self.n_qubits, self.n_inputs,
                                                 self.n_weights, _lib.ENCODER[self.encoder], flags, C.byref(out))
 
     def generic(self) -> "Circuit":
         """The same gate list, pinned to the generic kernel family."""
         return Circuit(self.n_qubits, self.ops, self.n_inputs, self.n_weights, self.encoder, generic_only=True)
+
+    def pinned(self, variant: str) -> "Circuit":
+        """The same gate list, pinned to one kernel variant."""
+        return Circuit(self.n_qubits, self.ops, self.n_inputs, self.n_weights, self.encoder, variant=variant)
 
     def handle(self, device_index: int):
         """``qnn_circuit*`` for a CUDA device (created on first use, with that device current)."""
@@ -122,11 +131,12 @@ class Circuit:
 
     def __getstate__(self):
         return {"n_qubits": self.n_qubits, "n_inputs": self.n_inputs, "n_weights": self.n_weights,
-                "encoder": self.encoder, "ops": self.ops, "generic_only": self.generic_only}
+                "encoder": self.encoder, "ops": self.ops, "generic_only": self.generic_only,
+                "variant": self.variant}
 
     def __setstate__(self, st):
         self.__init__(st["n_qubits"], st["ops"], st["n_inputs"], st["n_weights"], st["encoder"],
-                      st.get("generic_only", False))
+                      st.get("generic_only", False), st.get("variant"))
 
     def __repr__(self):
         return (f"Circuit(n_qubits={self.n_qubits}, n_ops={len(self.ops)}, n_inputs={self.n_inputs}, "

@@ -68,7 +68,7 @@ extern "C" int qnn_circuit_create_ex(const qnn_op* ops, int32_t n_ops, int32_t n
                                      int32_t n_weights, int32_t encoder, uint32_t flags, qnn_circuit** out) {
   if (!out) { qnn_set_error("qnn_circuit_create: out is NULL"); return QNN_ERR_INVALID; }
   *out = nullptr;
-  if (flags & ~(uint32_t)QNN_CREATE_GENERIC_ONLY) { qnn_set_error("qnn_circuit_create_ex: unknown flags 0x%x", flags); return QNN_ERR_INVALID; }
+  if (flags & ~(uint32_t)(QNN_CREATE_GENERIC_ONLY | QNN_CREATE_WIDE_ONLY | QNN_CREATE_NARROW_ONLY | QNN_CREATE_16_PER_THREAD)) { qnn_set_error("qnn_circuit_create_ex: unknown flags 0x%x", flags); return QNN_ERR_INVALID; }
   if (n_qubits < 1 || n_qubits > QNN_MAX_QUBITS) {
     qnn_set_error("n_qubits=%d outside [1, %d]", n_qubits, QNN_MAX_QUBITS);
     return QNN_ERR_INVALID;
@@ -142,8 +142,13 @@ extern "C" int qnn_circuit_create_ex(const qnn_op* ops, int32_t n_ops, int32_t n
   { std::vector<int32_t> fill(ptr.begin(), ptr.end() - 1);
     for (int s = 0; s < c->n_slots; ++s) if (c->slot_w[s] >= 0) idx[fill[c->slot_w[s]]++] = s; }
 
+  c->flags = flags;
   c->vm = new (std::nothrow) vm::Program();
-  if (c->vm) vm::compile(c, c->vm);
+  if (c->vm) vm::compile(c, c->vm, (flags & QNN_CREATE_16_PER_THREAD) ? 4 : vm::kR);
+  if (n_qubits <= 8 && encoder == QNN_ENC_NONE && !(flags & (QNN_CREATE_WIDE_ONLY | QNN_CREATE_16_PER_THREAD))) {
+    c->vm_narrow = new (std::nothrow) vm::Program();
+    if (c->vm_narrow) vm::compile(c, c->vm_narrow, 3);
+  }
 
   cudaError_t e = cudaGetDevice(&c->device);
   if (e != cudaSuccess) {
@@ -167,11 +172,13 @@ extern "C" int qnn_circuit_create_ex(const qnn_op* ops, int32_t n_ops, int32_t n
     qnn_circuit_destroy(c);
     return QNN_ERR_CUDA;
   }
-  if (c->vm && c->vm->ok) {
-    int rc = vm::upload(c->vm, n_weights);
-    if (rc != QNN_OK) { qnn_circuit_destroy(c); return rc; }
-    c->use_vm = !(flags & QNN_CREATE_GENERIC_ONLY);
+  for (vm::Program* prog : {c->vm, c->vm_narrow}) {
+    if (prog && prog->ok) {
+      int rc = vm::upload(prog, n_weights);
+      if (rc != QNN_OK) { qnn_circuit_destroy(c); return rc; }
+    }
   }
+  c->use_vm = !(flags & QNN_CREATE_GENERIC_ONLY);
   *out = c;
   return QNN_OK;
 }
@@ -182,6 +189,7 @@ extern "C" void qnn_circuit_destroy(qnn_circuit* c) {
   if (c->d_slot_ptr) cudaFree(c->d_slot_ptr);
   if (c->d_slot_idx) cudaFree(c->d_slot_idx);
   if (c->vm) { vm::release(c->vm); delete c->vm; }
+  if (c->vm_narrow) { vm::release(c->vm_narrow); delete c->vm_narrow; }
   delete c;
 }
 
@@ -191,7 +199,10 @@ extern "C" int32_t qnn_circuit_n_weights(const qnn_circuit* c) { return c ? c->n
 
 extern "C" size_t qnn_circuit_describe(const qnn_circuit* c, char* buf, size_t len) {
   if (!c || !c->vm) return 0;
-  const std::string s = vm::describe(*c->vm);
+  // the program a large batch runs; circuits that only the narrow variant takes (n = 3, 4) describe that one
+  const bool narrow_ok = c->vm_narrow && c->vm_narrow->ok;
+  const vm::Program* prog = (narrow_ok && (!c->vm->ok || (c->flags & QNN_CREATE_NARROW_ONLY))) ? c->vm_narrow : c->vm;
+  const std::string s = vm::describe(*prog);
   if (buf && len > 0) {
     const size_t k = std::min(len - 1, s.size());
     memcpy(buf, s.data(), k);
@@ -202,14 +213,25 @@ extern "C" size_t qnn_circuit_describe(const qnn_circuit* c, char* buf, size_t l
 
 // Which kernel family serves (circuit, B): the register-resident VM when the circuit lowered to it
 // and its tables fit in shared memory, otherwise the generic interpreter.
-static bool vm_plan(const qnn_circuit* c, int64_t B, vm::Plan* pl) {
-  return c->use_vm && c->vm && vm::plan(c, *c->vm, B, pl);
+// The narrow variant (8 amplitudes per thread, a warp carries 256) serves batches that would leave most warp slots
+// of the wide variant (32 per thread, 1024 per warp) empty: fewer than a quarter of the backward pass's warp slots
+// (measured cross-over, profiles/experiments/variants.py: n = 6 at B = 16,384 and n = 8 at B = 4,096 run alike).
+static const vm::Program* vm_plan(const qnn_circuit* c, int64_t B, vm::Plan* pl) {
+  if (!c->use_vm) return nullptr;
+  const bool wide_ok = c->vm && c->vm->ok, narrow_ok = c->vm_narrow && c->vm_narrow->ok;
+  bool narrow = narrow_ok && !wide_ok;
+  if (narrow_ok && wide_ok) {
+    const int64_t spw = c->vm->wb ? 1 : (32 >> c->vm->tb);
+    narrow = (c->flags & QNN_CREATE_NARROW_ONLY) || (B + spw - 1) / spw <= (int64_t)c->num_sm * 2;
+  }
+  const vm::Program* prog = narrow ? c->vm_narrow : c->vm;
+  return (prog && vm::plan(c, *prog, B, pl)) ? prog : nullptr;
 }
 
 extern "C" const char* qnn_circuit_plan(const qnn_circuit* c, int64_t B) {
   if (!c) return "";
   vm::Plan vp;
-  if (vm_plan(c, B, &vp)) return "vm-register";
+  if (const vm::Program* prog = vm_plan(c, B, &vp)) return prog->kr == 3 ? "vm-register-narrow" : prog->kr == 4 ? "vm-register-16" : "vm-register";
   GenericPlan p;
   generic_plan(c, B, &p);
   return p.name;   // a string literal
@@ -218,13 +240,13 @@ extern "C" const char* qnn_circuit_plan(const qnn_circuit* c, int64_t B) {
 extern "C" int32_t qnn_forward_launches(const qnn_circuit* c, int64_t B) {
   if (!c) return 0;
   vm::Plan vp;
-  if (vm_plan(c, B, &vp)) return 2;
+  if (const vm::Program* prog = vm_plan(c, B, &vp)) return vm::inline_prep(*prog) ? 1 : 2;
   return 1 + (c->n_coef > 0 ? 1 : 0);
 }
 extern "C" int32_t qnn_backward_launches(const qnn_circuit* c, int64_t B) {
   if (!c) return 0;
   vm::Plan vp;
-  if (vm_plan(c, B, &vp)) return 2 + (c->n_weights > 0 ? 1 : 0);
+  if (const vm::Program* prog = vm_plan(c, B, &vp)) return (vm::inline_prep(*prog) ? 1 : 2) + (c->n_weights > 0 ? 1 : 0);
   return 1 + (c->n_coef > 0 ? 1 : 0) + (c->n_weights > 0 ? 1 : 0);
 }
 
@@ -263,7 +285,8 @@ int qnn_check_common(const char* fn, const qnn_circuit* c, const float* x, const
 extern "C" size_t qnn_state_bytes(const qnn_circuit* c, int64_t B) {
   if (!c || B <= 0) return 0;
   vm::Plan vp;
-  return vm_plan(c, B, &vp) ? vm::state_bytes(*c->vm, B) : 0;
+  const vm::Program* prog = vm_plan(c, B, &vp);
+  return prog ? vm::state_bytes(*prog, B) : 0;
 }
 
 static int forward_impl(const char* fn, const qnn_circuit* c, const float* x, const float* w, float* y, float* state,
@@ -277,7 +300,7 @@ static int forward_impl(const char* fn, const qnn_circuit* c, const float* x, co
     return QNN_ERR_WORKSPACE;
   }
   vm::Plan vp;
-  if (vm_plan(c, B, &vp)) return vm::forward(c, *c->vm, vp, x, w, y, B, workspace, state, static_cast<cudaStream_t>(cuda_stream));
+  if (const vm::Program* prog = vm_plan(c, B, &vp)) return vm::forward(c, *prog, vp, x, w, y, B, workspace, state, static_cast<cudaStream_t>(cuda_stream));
   if (state) { qnn_set_error("%s: this circuit runs on the generic kernels, which keep no state (qnn_state_bytes() is 0)", fn); return QNN_ERR_UNSUPPORTED; }
   GenericPlan p;
   generic_plan(c, B, &p);
@@ -297,7 +320,7 @@ static int backward_impl(const char* fn, const qnn_circuit* c, const float* x, c
     return QNN_ERR_WORKSPACE;
   }
   vm::Plan vp;
-  if (vm_plan(c, B, &vp)) return vm::backward(c, *c->vm, vp, x, w, gy, gx, gw, B, workspace, state, static_cast<cudaStream_t>(cuda_stream));
+  if (const vm::Program* prog = vm_plan(c, B, &vp)) return vm::backward(c, *prog, vp, x, w, gy, gx, gw, B, workspace, state, static_cast<cudaStream_t>(cuda_stream));
   if (state) { qnn_set_error("%s: this circuit runs on the generic kernels, which keep no state (qnn_state_bytes() is 0)", fn); return QNN_ERR_UNSUPPORTED; }
   GenericPlan p;
   generic_plan(c, B, &p);

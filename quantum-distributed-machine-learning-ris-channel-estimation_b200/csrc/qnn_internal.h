@@ -39,7 +39,10 @@ struct qnn_circuit {
   int32_t* d_slot_idx = nullptr;
   int num_sm = 148;               // SM count of `device` (cudaDevAttrMultiProcessorCount), read at creation
   vm::Program* vm = nullptr;      // register-resident program (qnn_vm.h); vm->ok says whether it applies
-  bool use_vm = false;            // vm->ok and the circuit was not created with QNN_CREATE_GENERIC_ONLY
+  vm::Program* vm_narrow = nullptr;  // the same circuit with 8 amplitudes per thread (n <= 8): small batches spread over
+                                  //   four times as many warps; chosen per call by the batch size
+  bool use_vm = false;            // the circuit was not created with QNN_CREATE_GENERIC_ONLY
+  uint32_t flags = 0;             // creation flags
 };
 
 // SM count of the current device, cached per device ordinal (148 when it cannot be read).

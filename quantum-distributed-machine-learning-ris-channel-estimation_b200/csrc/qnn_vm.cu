@@ -3,6 +3,9 @@
 #include "qnn_vm_kernel.cuh"
 
 namespace vm {
+// Narrow variants whose tables all live in shared memory make them in the kernel's prologue (VmArgs::inline_prep).
+bool inline_prep(const Program& p) { return p.kr < kR && p.wb == 0; }
+
 namespace {
 
 // Layout of the shared-memory tables (byte offsets from their base); `total` is what they need.
@@ -21,8 +24,9 @@ TableLayout table_layout(const Program& p, int n_inputs, int warps, bool bwd, bo
   t.diags = take(p.diags.size() * sizeof(DiagDesc));
   t.coef = take(p.coef_ops.size() * 8 * sizeof(float));
   align256();
-  t.big = p.wb == 0 ? take((size_t)p.n_big_tables * 32 * G * sizeof(float2)) : 0u;
-  t.small = take((size_t)p.n_small_tables * 32 * sizeof(float2));
+  const size_t NA = (size_t)1 << p.kr;                      // amplitudes per thread
+  t.big = p.wb == 0 ? take((size_t)p.n_big_tables * NA * G * sizeof(float2)) : 0u;
+  t.small = take((size_t)p.n_small_tables * NA * sizeof(float2));
   t.xcoef = take((size_t)warps * spw * std::max(n_inputs, 1) * sizeof(float2));
   t.red = take((size_t)warps * 16 * sizeof(float));
   if (bwd) {
@@ -43,8 +47,9 @@ size_t smem_bytes(const Program& p, int n_inputs, int warps, bool bwd, bool clus
     for (const Exchange& X : p.exchanges) has_shared = has_shared || X.pad[0] != 0;
     return table_bytes(p, n_inputs, warps, bwd, true) + (has_shared ? 2 * 65536 : 0) + 64;
   }
-  const size_t group_buf = (size_t)8192 << p.wb;
-  return group_buf + (size_t)warps * 8192 + table_bytes(p, n_inputs, warps, bwd, false) + 64;
+  const size_t warp_buf = (size_t)256 << p.kr;               // 32 lanes x 2^kr amplitudes x 8 bytes
+  const size_t group_buf = warp_buf << p.wb;
+  return group_buf + (size_t)warps * warp_buf + table_bytes(p, n_inputs, warps, bwd, false) + 64;
 }
 
 // ---- per-call tables: gate coefficients (double-precision trig) and merged diagonals -----------------
@@ -53,35 +58,19 @@ size_t smem_bytes(const Program& p, int n_inputs, int warps, bool bwd, bool clus
 constexpr int kPrepThreads = 128, kPrepChunk = 1024, kPrepTermTile = 64;
 __global__ void __launch_bounds__(kPrepThreads)
 k_vm_prep(const DevOp* __restrict__ coef_ops, int n_coef, const DiagDesc* __restrict__ diags, int n_diags,
-          const DiagTerm* __restrict__ terms, const float* __restrict__ w, int tb, int wbits, float* __restrict__ coef,
+          const DiagTerm* __restrict__ terms, const float* __restrict__ w, int tb, int wbits, int kr, float* __restrict__ coef,
           float2* __restrict__ big, float2* __restrict__ small, int coef_blocks, int chunks) {
   if ((int)blockIdx.x < coef_blocks) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_coef) return;
-    const DevOp op = coef_ops[i];
-    double a[3] = {0, 0, 0};
-    for (int k = 0; k < op.nang; ++k) a[k] = (op.src[k] == QNN_SRC_CONST) ? (double)op.value[k] : (double)w[op.src[k]];
-    // row: [al, be, m0, 0, cos l, sin l, cos p, sin p]  (RY rows use al, be only)
-    const double pi = 3.14159265358979323846;
-    double phi = 0.5 * a[0];
-    const double k = rint(phi / pi);
-    phi -= k * pi;
-    float* row = coef + (size_t)i * QNN_COEF_STRIDE;
-    row[0] = (float)(-tan(0.5 * phi));
-    row[1] = (float)sin(phi);
-    row[2] = (((long long)k) & 1LL) ? -1.f : 1.f;
-    row[3] = 0.f;
-    double sl, cl, sp, cp;
-    sincos(a[2], &sl, &cl);
-    sincos(a[1], &sp, &cp);
-    row[4] = (float)cl; row[5] = (float)sl; row[6] = (float)cp; row[7] = (float)sp;
+    if (i < n_coef) make_coef_row(coef_ops[i], w, coef + (size_t)i * QNN_COEF_STRIDE);
     return;
   }
   const int d = ((int)blockIdx.x - coef_blocks) / chunks, chunk = ((int)blockIdx.x - coef_blocks) % chunks;
   if (d >= n_diags) return;
   const DiagDesc D = diags[d];
   const int G = 32 << wbits;
-  const int entries = D.is_reg ? 32 : 32 * G;
+  const int NA = 1 << kr;
+  const int entries = D.is_reg ? NA : NA * G;
   if (chunk * kPrepChunk >= entries) return;
   const unsigned tmask = wbits ? (unsigned)(G - 1) : ((1u << tb) - 1u);   // thread bits of one sample
   // the terms of this diagonal, staged once per CTA: angle (the weight read happens here) and bit masks
@@ -108,7 +97,7 @@ k_vm_prep(const DevOp* __restrict__ coef_ops, int n_coef, const DiagDesc* __rest
     for (int q = 0; q < kPer; ++q) {
       const int e = chunk * kPrepChunk + q * kPrepThreads + threadIdx.x;
       const int j = D.is_reg ? e : (e / G), t = D.is_reg ? 0 : (e % G);
-      const unsigned p = (unsigned)j | (((unsigned)t & tmask) << kR);
+      const unsigned p = (unsigned)j | (((unsigned)t & tmask) << kr);
       double acc = ang[q];
       for (int k = 0; k < nt; ++k) {
         if (s_kind[k] == 0) acc += (p & s_m0[k]) ? s_phi[k] : -s_phi[k];
@@ -124,7 +113,7 @@ k_vm_prep(const DevOp* __restrict__ coef_ops, int n_coef, const DiagDesc* __rest
     double sn, cs;
     sincos(ang[q], &sn, &cs);
     const float2 v = make_float2((float)cs, (float)sn);
-    if (D.is_reg) small[(size_t)D.table * 32 + e] = v; else big[(size_t)D.table * 32 * G + e] = v;
+    if (D.is_reg) small[(size_t)D.table * NA + e] = v; else big[(size_t)D.table * NA * G + e] = v;
   }
 }
 
@@ -163,9 +152,11 @@ void fill_args(const qnn_circuit* c, const Program& p, const Plan& pl, void* ws,
   a->diags = p.d_diags; a->n_diags = (int)p.diags.size();
   a->coef = reinterpret_cast<const float*>(wsb); a->n_coef = (int)p.coef_ops.size();
   a->big = reinterpret_cast<const float2*>(wsb + pl.ws_coef); a->n_big = p.n_big_tables;
-  a->small = a->big + (size_t)p.n_big_tables * 32 * G; a->n_small = p.n_small_tables;
+  a->small = a->big + ((size_t)p.n_big_tables << p.kr) * G; a->n_small = p.n_small_tables;
   a->n = p.n; a->tb = p.tb; a->wb = p.wb; a->n_inputs = c->n_inputs; a->n_acc = p.n_acc;
   a->cluster = pl.cluster;
+  a->inline_prep = inline_prep(p) ? 1 : 0;
+  a->coef_ops = p.d_coef_ops; a->terms = p.d_terms; a->n_terms = (int)p.terms.size();
   a->amplitude = p.amplitude ? 1 : 0;
   a->n_angle = p.amplitude ? 0 : c->n_inputs;
   for (int w = 0; w < 16; ++w) a->init_bit_of_wire[w] = w < p.n ? (int8_t)p.initial_bit_of_wire[w] : 0;
@@ -186,12 +177,13 @@ void fill_args(const qnn_circuit* c, const Program& p, const Plan& pl, void* ws,
 }
 
 int launch_prep(const Program& p, const float* w, const VmArgs& a, cudaStream_t st) {
+  if (inline_prep(p)) return QNN_OK;
   const int coef_blocks = ((int)p.coef_ops.size() + kPrepThreads - 1) / kPrepThreads;
-  const int chunks = p.n_big_tables > 0 ? std::max(1, (1024 << p.wb) / kPrepChunk) : 1;   // CTAs per diagonal table
+  const int chunks = p.n_big_tables > 0 ? std::max(1, ((32 << p.kr) << p.wb) / kPrepChunk) : 1;   // CTAs per diagonal table
   const int blocks = coef_blocks + (int)p.diags.size() * chunks;
   if (blocks == 0) return QNN_OK;
   k_vm_prep<<<blocks, kPrepThreads, 0, st>>>(p.d_coef_ops, (int)p.coef_ops.size(), p.d_diags, (int)p.diags.size(), p.d_terms, w, p.tb,
-                                             p.wb, const_cast<float*>(a.coef), const_cast<float2*>(a.big),
+                                             p.wb, p.kr, const_cast<float*>(a.coef), const_cast<float2*>(a.big),
                                              const_cast<float2*>(a.small), coef_blocks, chunks);
   QNN_CUDA_CHECK(cudaGetLastError());
   return QNN_OK;
@@ -205,7 +197,7 @@ static int64_t n_batches(const Program& p, int64_t B) {
 }
 
 size_t state_bytes(const Program& p, int64_t B) {
-  return (size_t)n_batches(p, B) * ((size_t)kWarpAmps << p.wb) * sizeof(float2);
+  return (size_t)n_batches(p, B) * (((size_t)32 << p.kr) << p.wb) * sizeof(float2);
 }
 
 bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
@@ -243,10 +235,11 @@ bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
     out->smem_bwd = sb;
     const int64_t groups_per_cta = bwd_warps >> p.wb;
     const int64_t ctas = (n_batches(p, B) + groups_per_cta - 1) / groups_per_cta;
-    out->grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, c->num_sm));   // backward: one CTA per SM
+    // backward: one CTA per SM (255 registers); the narrow variants fit two
+    out->grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, (int64_t)c->num_sm * (p.kr < kR ? 2 : 1)));
   }
   out->ws_coef = align256(std::max<size_t>(p.coef_ops.size(), 1) * QNN_COEF_STRIDE * sizeof(float));
-  out->ws_diag = align256(((size_t)p.n_big_tables * (1024u << p.wb) + (size_t)p.n_small_tables * 32 + 1) * sizeof(float2));
+  out->ws_diag = align256(((size_t)p.n_big_tables * (((size_t)32 << p.kr) << p.wb) + ((size_t)p.n_small_tables << p.kr) + 1) * sizeof(float2));
   out->ws_partial = align256((size_t)out->grid * std::max(p.n_acc, 1) * sizeof(float));
   return true;
 }
@@ -292,38 +285,41 @@ void release(Program* p) {
   p->d_exchanges = nullptr; p->d_xbase = nullptr; p->d_slots = nullptr; p->d_slot_ptr = nullptr; p->d_slot_idx = nullptr;
 }
 
+// The kernel instantiation for (register bits, geometry, encoder).
+static int launch_variant(const Program& p, const Plan& pl, bool bwd, bool state_on, const LaunchCfg& lc, const VmArgs& a) {
+  if (p.kr == 3) return launch_g0_k3(bwd, state_on, lc, a);
+  if (p.kr == 4) return p.wb > 0 ? launch_g1_k4(bwd, state_on, lc, a) : launch_g0_k4(bwd, state_on, lc, a);
+  if (pl.cluster > 0) return launch_g2(bwd, state_on, lc, a);
+  if (p.wb > 0) return launch_g1(bwd, state_on, lc, a);
+  return p.amplitude ? launch_g0a(bwd, state_on, lc, a) : launch_g0(bwd, state_on, lc, a);
+}
+
 int forward(const qnn_circuit* c, const Program& p, const Plan& pl, const float* x, const float* w, float* y,
             int64_t B, void* ws, float* state, cudaStream_t st) {
   VmArgs a{};
   fill_args(c, p, pl, ws, false, &a);
-  a.x = x; a.y = y; a.B = B; a.state = reinterpret_cast<float4*>(state);
+  a.x = x; a.y = y; a.B = B; a.state = reinterpret_cast<float4*>(state); a.w = w;
   int rc = launch_prep(p, w, a, st);
   if (rc) return rc;
   int grid = pl.grid;
   if (pl.cluster == 0) {
     const int64_t groups_per_cta = (pl.fwd_threads / 32) >> p.wb;
     const int64_t ctas = (n_batches(p, B) + groups_per_cta - 1) / groups_per_cta;
-    grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, c->num_sm));
+    grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, (int64_t)c->num_sm * (p.kr < kR ? 2 : 1)));
   }
   const LaunchCfg lc{grid, pl.fwd_threads, pl.cluster, pl.smem_fwd, st};
-  const bool state_on = a.state != nullptr;
-  if (pl.cluster > 0) return launch_g2(false, state_on, lc, a);
-  if (p.wb > 0) return launch_g1(false, state_on, lc, a);
-  return p.amplitude ? launch_g0a(false, state_on, lc, a) : launch_g0(false, state_on, lc, a);
+  return launch_variant(p, pl, false, a.state != nullptr, lc, a);
 }
 
 int backward(const qnn_circuit* c, const Program& p, const Plan& pl, const float* x, const float* w,
              const float* gy, float* gx, float* gw, int64_t B, void* ws, const float* state, cudaStream_t st) {
   VmArgs a{};
   fill_args(c, p, pl, ws, true, &a);
-  a.x = x; a.gy = gy; a.gx = gx; a.B = B; a.state = reinterpret_cast<float4*>(const_cast<float*>(state));
+  a.x = x; a.gy = gy; a.gx = gx; a.B = B; a.state = reinterpret_cast<float4*>(const_cast<float*>(state)); a.w = w;
   int rc = launch_prep(p, w, a, st);
   if (rc) return rc;
   const LaunchCfg lc{pl.grid, kBwdThreads, pl.cluster, pl.smem_bwd, st};
-  const bool state_on = a.state != nullptr;
-  if (pl.cluster > 0) rc = launch_g2(true, state_on, lc, a);
-  else if (p.wb > 0) rc = launch_g1(true, state_on, lc, a);
-  else rc = p.amplitude ? launch_g0a(true, state_on, lc, a) : launch_g0(true, state_on, lc, a);
+  rc = launch_variant(p, pl, true, a.state != nullptr, lc, a);
   if (rc) return rc;
   if (c->n_weights > 0) {
     k_vm_finalize<<<c->n_weights, 128, 0, st>>>(a.partial, pl.grid, p.n_acc, p.d_slots, p.d_slot_ptr, p.d_slot_idx, gw);

@@ -91,8 +91,9 @@ struct Program {
   bool ok = false;
   std::string why_not;           // when !ok: why the VM does not take this circuit (generic path used)
   bool amplitude = false;        // amplitude encoder: the (normalised) input row is the initial state (n <= 10)
-  int n = 0, tb = 0;             // tb = n - 5 thread bits
-  int wb = 0;                    // warp bits: max(0, n - 10); a group is 2^wb warps
+  int kr = kR;                   // register bits: every thread keeps 2^kr amplitudes (5; 3 or 4 in the narrow variants)
+  int n = 0, tb = 0;             // tb = n - kr thread bits
+  int wb = 0;                    // warp bits: max(0, n - kr - 5); a group is 2^wb warps
   std::vector<MicroOp> ops;      // forward order, MOP_END-terminated
   std::vector<DevOp> coef_ops;   // recipes (gate kind + angle sources), one per 8-float coefficient row
   std::vector<DiagTerm> terms;
@@ -117,7 +118,7 @@ struct Program {
 };
 
 // Lower a validated circuit.  Never fails hard: sets ok=false + why_not when out of the VM's scope.
-void compile(const qnn_circuit* c, Program* out);
+void compile(const qnn_circuit* c, Program* out, int kr = kR);
 std::string describe(const Program& p);   // JSON, for tests and introspection
 
 struct Plan {
@@ -129,6 +130,7 @@ struct Plan {
   size_t ws_coef, ws_diag, ws_partial;   // bytes (each 256-aligned)
 };
 bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out);
+bool inline_prep(const Program& p);      // the kernel makes its per-call tables itself: no k_vm_prep launch
 int upload(Program* p, int n_weights);
 void release(Program* p);
 size_t state_bytes(const Program& p, int64_t B);

@@ -110,6 +110,7 @@ struct Builder {
   const qnn_circuit* c;
   Program* P;
   int n, tb;
+  int kr = kr;             // register bits of this program (5, or 3 / 4 for the narrow variants)
   bool no_local = false;   // cluster geometry: never use the shared-memory (local) exchange
   bool use_dsmem = true;   // cluster geometry: exchanges that cross CTAs go through distributed shared memory (else L2)
   int policy = 0;   // how "apply the pending diagonal" and "exchange" are ordered when both are possible
@@ -268,9 +269,9 @@ struct Builder {
       t.src = it.src[0]; t.value = it.value[0];
       t.bit0 = bit_of(it.w0);
       t.bit1 = it.kind == IT_RZ ? -1 : bit_of(it.w1);
-      if (t.bit0 >= kR || t.bit1 >= kR) reg_only = false;
+      if (t.bit0 >= kr || t.bit1 >= kr) reg_only = false;
       if (t.kind == 0 && t.src >= 0) {
-        int32_t& a = t.bit0 < kR ? D.acc_reg[t.bit0] : D.acc_thr[t.bit0 - kR];
+        int32_t& a = t.bit0 < kr ? D.acc_reg[t.bit0] : D.acc_thr[t.bit0 - kr];
         if (a < 0) a = P->n_acc++;
         P->slots.push_back(GradSlot{t.src, a});
       }
@@ -297,10 +298,10 @@ struct Builder {
       case IT_CP: return (row_unit(it.w0) && row_unit(it.w1)) ? ST_OK : ST_BLOCKED;
       case IT_CNOT: return pending_on(it.w1) ? ST_NEEDS_FLUSH : ST_OK;
       case IT_REAL:
-        if (!clean(it.w0) || bit_of(it.w0) >= kR) return ST_BLOCKED;
+        if (!clean(it.w0) || bit_of(it.w0) >= kr) return ST_BLOCKED;
         return pending_on(it.w0) ? ST_NEEDS_FLUSH : ST_OK;
       case IT_CGEN:
-        if (!clean(it.w1) || bit_of(it.w1) >= kR || !row_unit(it.w0)) return ST_BLOCKED;
+        if (!clean(it.w1) || bit_of(it.w1) >= kr || !row_unit(it.w0)) return ST_BLOCKED;
         return pending_on(it.w1) ? ST_NEEDS_FLUSH : ST_OK;
     }
     return ST_BLOCKED;
@@ -324,7 +325,7 @@ struct Builder {
         rowmask[it.w1] ^= rowmask[it.w0];
         return true;
       case IT_REAL: {
-        if (!clean(it.w0) || bit_of(it.w0) >= kR) return false;
+        if (!clean(it.w0) || bit_of(it.w0) >= kr) return false;
         if (pending_on(it.w0)) flush_diag();
         MicroOp m{};
         m.a = bit_of(it.w0); m.acc = -1;
@@ -338,13 +339,13 @@ struct Builder {
         return true;
       }
       case IT_CGEN: {
-        if (!clean(it.w1) || bit_of(it.w1) >= kR || !row_unit(it.w0)) return false;
+        if (!clean(it.w1) || bit_of(it.w1) >= kr || !row_unit(it.w0)) return false;
         if (pending_on(it.w1)) flush_diag();
         MicroOp m{};
         m.a = bit_of(it.w1); m.acc = -1;
         const int cb = bit_of(it.w0);
-        if (cb < kR) { m.kind = MOP_CU3_L; m.b = cb; }
-        else { m.kind = MOP_CU3_P; m.aux = 1 << (cb - kR); }   // thread-bit mask (lanes, then warps)
+        if (cb < kr) { m.kind = MOP_CU3_L; m.b = cb; }
+        else { m.kind = MOP_CU3_P; m.aux = 1 << (cb - kr); }   // thread-bit mask (lanes, then warps)
         if (it.inline_post) m.b |= kCu3InlinePost;
         m.idx = new_coef_row(QNN_CU3, it.src, it.value, 3);
         bool any_w = false;
@@ -366,12 +367,12 @@ struct Builder {
   // `global` false: the wanted wires take the register bits, the wires they displace take the vacated bits,
   // every other clean wire stays.  `global` true: the CTA bits receive the wires that are needed last.
   void choose_layout_cluster(int* bit_of_wire, const std::vector<int>& order_in, bool global) {
-    std::vector<int> order(order_in.begin(), order_in.begin() + kR);
+    std::vector<int> order(order_in.begin(), order_in.begin() + kr);
     if (global && all_clean())
-      std::stable_partition(order.begin(), order.end(), [&](int w) { const int b = ctz(rowmask[w]); return b >= kR && b < 10; });
+      std::stable_partition(order.begin(), order.end(), [&](int w) { const int b = ctz(rowmask[w]); return b >= kr && b < kr + 5; });
     std::vector<int> nb(n, -1);
     uint32_t taken = 0;
-    for (int r = 0; r < kR; ++r) { nb[order[r]] = r; taken |= 1u << r; }
+    for (int r = 0; r < kr; ++r) { nb[order[r]] = r; taken |= 1u << r; }
     auto next_use = [&](int w) {
       for (size_t i = 0; i < items.size(); ++i)
         if (!items[i].done && (items[i].kind == IT_REAL || items[i].kind == IT_CGEN) && (items[i].w0 == w || items[i].w1 == w))
@@ -395,16 +396,16 @@ struct Builder {
   void choose_layout(int* bit_of_wire, bool global = true) {
     std::vector<int> order;
     auto add = [&](int w) { if (w >= 0 && std::find(order.begin(), order.end(), w) == order.end()) order.push_back(w); };
-    for (size_t i = 0; i < items.size() && (int)order.size() < kR; ++i) {
+    for (size_t i = 0; i < items.size() && (int)order.size() < kr; ++i) {
       if (items[i].done) continue;
       if (items[i].kind == IT_REAL) add(items[i].w0);
       else if (items[i].kind == IT_CGEN) add(items[i].w1);
     }
-    for (size_t i = 0; i < items.size() && (int)order.size() < kR; ++i)
+    for (size_t i = 0; i < items.size() && (int)order.size() < kr; ++i)
       if (!items[i].done && items[i].kind == IT_CGEN) add(items[i].w0);
-    for (int w = 0; w < n && (int)order.size() < kR; ++w)
-      if (is_unit(rowmask[w]) && ctz(rowmask[w]) < kR) add(w);
-    for (int w = 0; w < n && (int)order.size() < kR; ++w) add(w);
+    for (int w = 0; w < n && (int)order.size() < kr; ++w)
+      if (is_unit(rowmask[w]) && ctz(rowmask[w]) < kr) add(w);
+    for (int w = 0; w < n && (int)order.size() < kr; ++w) add(w);
     if (P->wb > 3) {
       // (global exchanges: wires that now sit on lane bits take the low register bits, so that after the
       // exchange a thread's registers 0..3 are consecutive slots of the L2 buffer, one 32-byte sector)
@@ -412,8 +413,8 @@ struct Builder {
       return;
     }
     std::vector<bool> used(n, false);
-    for (int r = 0; r < kR; ++r) { bit_of_wire[order[r]] = r; used[order[r]] = true; }
-    int b = kR;
+    for (int r = 0; r < kr; ++r) { bit_of_wire[order[r]] = r; used[order[r]] = true; }
+    int b = kr;
     for (int w = 0; w < n; ++w) if (!used[w]) bit_of_wire[w] = b++;
   }
 
@@ -473,15 +474,15 @@ struct Builder {
   void push_exchange_tables(Exchange& X, const uint32_t* scol, const uint32_t* rcol) {
     const int G = 32 << P->wb;
     X.base = (uint32_t)P->xbase.size();
-    for (int v = 0; v < 32; ++v) {
+    for (int v = 0; v < (1 << kr); ++v) {
       uint32_t wo = 0, ro = 0;
-      for (int i = 0; i < 5; ++i) if ((v >> i) & 1) { wo ^= scol[i]; ro ^= rcol[i]; }
+      for (int i = 0; i < kr; ++i) if ((v >> i) & 1) { wo ^= scol[i]; ro ^= rcol[i]; }
       X.woff[v] = wo * 8; X.roff[v] = ro * 8;
     }
     for (int side = 0; side < 2; ++side)
       for (int t = 0; t < G; ++t) {
         uint32_t b = 0;
-        for (int i = 0; i < 5 + P->wb; ++i) if ((t >> i) & 1) b ^= side ? rcol[5 + i] : scol[5 + i];
+        for (int i = 0; i < 5 + P->wb; ++i) if ((t >> i) & 1) b ^= side ? rcol[kr + i] : scol[kr + i];
         P->xbase.push_back(b * 8);
       }
   }
@@ -491,7 +492,7 @@ struct Builder {
     if (!invert(rowmask, n, inv_col)) { P->why_not = "internal: singular layout"; return false; }
     // Extended index of an amplitude inside a group's buffer: bits 0..4 register index, 5..9 lane,
     // 10.. warp-in-group.  For n < 10 the lanes above the sample's own are sample-in-warp bits and stay put.
-    const int E = 10 + P->wb;
+    const int E = kr + 5 + P->wb;
     // acol[b']: old extended index contributed by new extended bit b'
     uint32_t acol[16];
     for (int w = 0; w < n; ++w) acol[new_bit_of_wire[w]] = inv_col[w];
@@ -563,7 +564,7 @@ struct Builder {
       if (P->wb > 3 && !local) break;
       // shared-memory buffer: no bank conflicts within a half-warp, writing and reading
       uint32_t wlow[4], rlow[4];
-      for (int i = 0; i < 4; ++i) { wlow[i] = scol[5 + i] & 15u; rlow[i] = rcol[5 + i] & 15u; }
+      for (int i = 0; i < 4; ++i) { wlow[i] = scol[kr + i] & 15u; rlow[i] = rcol[kr + i] & 15u; }
       if (independent(wlow, 4) && independent(rlow, 4)) break;
     }
     Exchange X{};
@@ -583,34 +584,35 @@ struct Builder {
     const std::vector<MicroOp>& in = P->ops;
     for (size_t i = 0; i < in.size();) {
       auto distinct_bits = [&](int kind, bool need_acc) {
-        if (i + 5 > in.size()) return false;
+        if (i + kr > in.size()) return false;
         uint32_t seen = 0;
-        for (int k = 0; k < 5; ++k) {
+        for (int k = 0; k < kr; ++k) {
           const MicroOp& m = in[i + k];
           if (m.kind != kind || ((seen >> m.a) & 1u)) return false;
           if (need_acc && (m.acc != in[i].acc + k || m.idx != in[i].idx + k)) return false;
           seen |= 1u << m.a;
         }
-        return seen == 31u;
+        return seen == (1u << kr) - 1u;
       };
       if (distinct_bits(MOP_ROT, true)) {
         MicroOp m{};
         m.kind = MOP_ROT5; m.idx = in[i].idx; m.acc = in[i].acc;
-        for (int k = 0; k < 5; ++k) m.aux |= k << (3 * in[i + k].a);
+        for (int k = 0; k < kr; ++k) m.aux |= k << (3 * in[i + k].a);
         out.push_back(m);
-        i += 5;
+        i += kr;
         continue;
       }
       if (distinct_bits(MOP_ROT_X, false)) {
         MicroOp m{};
         m.kind = MOP_ROTX5; m.acc = -1;
-        for (int k = 0; k < 5; ++k) m.idx |= in[i + k].idx << (5 * in[i + k].a);
+        for (int k = 0; k < kr; ++k) m.idx |= in[i + k].idx << (5 * in[i + k].a);
         out.push_back(m);
-        i += 5;
+        i += kr;
         continue;
       }
-      bool chain = i + 4 <= in.size();
-      for (int k = 0; chain && k < 4; ++k) {
+      const int steps = kr - 1;                       // (target, control) = (1,0) ... (kr-1, kr-2)
+      bool chain = steps >= 2 && i + steps <= in.size();
+      for (int k = 0; chain && k < steps; ++k) {
         const MicroOp& m = in[i + k];
         chain = m.kind == MOP_CU3_L && m.a == k + 1 && (m.b & 7) == k && m.idx == in[i].idx + k && in[i].acc >= 0 &&
                 m.acc == in[i].acc + 3 * k;
@@ -618,9 +620,9 @@ struct Builder {
       if (chain) {
         MicroOp m{};
         m.kind = MOP_CU3_CHAIN; m.idx = in[i].idx; m.acc = in[i].acc;
-        for (int k = 0; k < 4; ++k) if (in[i + k].b & kCu3InlinePost) m.aux |= 1 << k;   // per-gate inline post-phase
+        for (int k = 0; k < steps; ++k) if (in[i + k].b & kCu3InlinePost) m.aux |= 1 << k;   // per-gate inline post-phase
         out.push_back(m);
-        i += 4;
+        i += steps;
         continue;
       }
       out.push_back(in[i++]);
@@ -660,10 +662,14 @@ struct Builder {
 
   bool run() {
     n = c->n_qubits;
-    tb = n - kR;
-    P->n = n; P->tb = tb; P->wb = n > 10 ? n - 10 : 0;
-    if (n < kMinQubits || n > kMaxQubits) { P->why_not = "n_qubits outside [5, 16]"; return false; }
+    tb = n - kr;
+    P->kr = kr;
+    P->n = n; P->tb = tb; P->wb = n > kr + 5 ? n - kr - 5 : 0;
+    if (kr == kR && (n < kMinQubits || n > kMaxQubits)) { P->why_not = "n_qubits outside [5, 16]"; return false; }
+    // narrow variants (fewer amplitudes per thread): whole samples per warp for kr = 3, up to one CTA per sample for kr = 4
+    if (kr != kR && (n < kr || n > (kr == 3 ? 8 : 12))) { P->why_not = "n_qubits outside the narrow variant's range"; return false; }
     P->amplitude = c->encoder == QNN_ENC_AMPLITUDE;
+    if (P->amplitude && kr != kR) { P->why_not = "amplitude encoder in a narrow variant"; return false; }
     if (P->amplitude && n > 10) { P->why_not = "amplitude encoder above 10 qubits"; return false; }
     if (!P->amplitude && c->n_inputs > 32) { P->why_not = "more than 32 angle input columns"; return false; }
     if (!lower_items()) return false;
@@ -702,8 +708,8 @@ struct Builder {
       if (f >= 0 && policy == 2 && items[f].kind == IT_CGEN) {     // ... only for two-qubit gates whose
         bool all_local = true;                                      //     pending terms are register-only
         for (int i : pending) {
-          if (bit_of(items[i].w0) >= kR) all_local = false;
-          if (items[i].w1 >= 0 && bit_of(items[i].w1) >= kR) all_local = false;
+          if (bit_of(items[i].w0) >= kr) all_local = false;
+          if (items[i].w1 >= 0 && bit_of(items[i].w1) >= kr) all_local = false;
         }
         if (all_local) flush_first = true;
       }
@@ -766,7 +772,7 @@ static double program_cost(const Program& p) {
   return cost;
 }
 
-void compile(const qnn_circuit* c, Program* out) {
+void compile(const qnn_circuit* c, Program* out, int kr) {
   // The scheduler is greedy; its one real choice (diagonal first or exchange first) is made by trying
   // each policy and keeping the cheapest program.
   Program best;
@@ -788,7 +794,7 @@ void compile(const qnn_circuit* c, Program* out) {
   for (int policy = 0; policy < 3; ++policy) {
     Program cand;
     Builder b{};
-    b.c = c; b.P = &cand; b.policy = policy; b.no_local = no_local != 0; b.use_dsmem = no_local == 0;
+    b.c = c; b.P = &cand; b.policy = policy; b.no_local = no_local != 0; b.use_dsmem = no_local == 0; b.kr = kr;
     if (!b.run()) {
       cand.ok = false;
       cand.ops.clear();
@@ -807,7 +813,7 @@ std::string describe(const Program& p) {
   o.precision(9);
   o << "{\"ok\": " << (p.ok ? "true" : "false") << ", \"why_not\": \"" << p.why_not << "\"";
   if (!p.ok) { o << "}"; return o.str(); }
-  o << ", \"amplitude\": " << (p.amplitude ? "true" : "false") << ", \"n\": " << p.n << ", \"tb\": " << p.tb << ", \"wb\": " << p.wb << ", \"n_acc\": " << p.n_acc;
+  o << ", \"amplitude\": " << (p.amplitude ? "true" : "false") << ", \"kr\": " << p.kr << ", \"n\": " << p.n << ", \"tb\": " << p.tb << ", \"wb\": " << p.wb << ", \"n_acc\": " << p.n_acc;
   auto arr = [&](const char* name, const int* v, int cnt) {
     o << ", \"" << name << "\": [";
     for (int i = 0; i < cnt; ++i) o << (i ? ", " : "") << v[i];
@@ -851,9 +857,9 @@ std::string describe(const Program& p) {
       o << "]";
     };
     tab("wbase", p.xbase.data() + X.base, G, true);
-    tab("woff", X.woff, 32, false);
+    tab("woff", X.woff, 1 << p.kr, false);
     tab("rbase", p.xbase.data() + X.base + G, G, false);
-    tab("roff", X.roff, 32, false);
+    tab("roff", X.roff, 1 << p.kr, false);
     o << ", \"local\": " << X.pad[0] << ", \"link\": " << X.pad[1] << "}";
   }
   o << "], \"slots\": [";

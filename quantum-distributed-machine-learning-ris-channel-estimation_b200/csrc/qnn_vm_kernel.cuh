@@ -24,7 +24,6 @@
 
 namespace vm {
 
-constexpr int NA = kAmps;  // 32
 
 struct VmArgs {
   const MicroOp* ops; int n_ops;            // including the END marker
@@ -48,7 +47,41 @@ struct VmArgs {
   const float* gy; float* gx; float* partial;  // backward; partial [grid][n_acc]
   float4* state;                            // optional: final psi of every warp-batch (forward writes, backward reads)
   long long B;
+  // narrow variants: the per-call tables (coefficient rows, diagonals) are made in the kernel's prologue by every
+  // CTA instead of by a k_vm_prep launch (small programs, small batches: the launch costs more than the work)
+  int inline_prep;
+  const DevOp* coef_ops; const DiagTerm* terms; const float* w; int n_terms;
 };
+
+// ---- per-call tables: gate coefficients and merged diagonals (double-precision trig) -------------------------
+// row: [al, be, m0, 0, cos l, sin l, cos p, sin p]  (RY rows use al, be only)
+__device__ __forceinline__ void make_coef_row(const DevOp& op, const float* __restrict__ w, float* row) {
+  double a[3] = {0, 0, 0};
+  for (int k = 0; k < op.nang; ++k) a[k] = (op.src[k] == QNN_SRC_CONST) ? (double)op.value[k] : (double)w[op.src[k]];
+  const double pi = 3.14159265358979323846;
+  double phi = 0.5 * a[0];
+  const double k = rint(phi / pi);
+  phi -= k * pi;
+  row[0] = (float)(-tan(0.5 * phi));
+  row[1] = (float)sin(phi);
+  row[2] = (((long long)k) & 1LL) ? -1.f : 1.f;
+  row[3] = 0.f;
+  double sl, cl, sp, cp;
+  sincos(a[2], &sl, &cl);
+  sincos(a[1], &sp, &cp);
+  row[4] = (float)cl; row[5] = (float)sl; row[6] = (float)cp; row[7] = (float)sp;
+}
+// phase angle of a merged diagonal at physical index p (register bits below, the sample's thread bits above)
+__device__ __forceinline__ double diag_angle(const DiagDesc& D, const DiagTerm* __restrict__ terms, const float* __restrict__ w, unsigned p) {
+  double ang = 0.0;
+  for (int t = 0; t < D.n_terms; ++t) {
+    const DiagTerm tm = terms[D.first_term + t];
+    const double v = (tm.src == QNN_SRC_CONST) ? (double)tm.value : (double)w[tm.src];
+    if (tm.kind == 0) ang += ((p >> tm.bit0) & 1u) ? 0.5 * v : -0.5 * v;
+    else if (((p >> tm.bit0) & 1u) && ((p >> tm.bit1) & 1u)) ang += tm.kind == 1 ? 3.14159265358979323846 : v;
+  }
+  return ang;
+}
 
 // ---- shared-memory access by 32-bit shared address (XOR addressing needs integer addresses) --------
 __device__ __forceinline__ void sts64(uint32_t addr, float a, float b) {
@@ -92,7 +125,7 @@ __device__ __forceinline__ float2 swp(float2 a) { return make_float2(a.y, a.x); 
 //   a0 += al*a1;  a1 += be*a0;  a0 += al*a1       al = -tan(phi/2), be = sin(phi)
 // 3 packed FMAs per amplitude pair, no temporaries; the inverse uses (-al, -be).  phi is range-reduced to
 // [-pi/2, pi/2] when the coefficients are made, so |al| = |tan(phi/2)| <= 1.
-template <int RB>
+template <int RB, int NA>
 __device__ __forceinline__ void rot(float2 (&st)[NA], float al, float be) {
 #pragma unroll
   for (int i = 0; i < NA / 2; ++i) {
@@ -107,7 +140,7 @@ __device__ __forceinline__ void rot_grad_acc(float2& v0, float2& v1, float2 p0, 
   v0 = __ffma2_rn(l1, p0, v0);
   v1 = __ffma2_rn(l0, p1, v1);
 }
-template <int RB>
+template <int RB, int NA>
 __device__ __forceinline__ float rot_grad(const float2 (&ps)[NA], const float2 (&ls)[NA]) {
   const float2 z = make_float2(0.f, 0.f);
   float2 v0[4] = {z, z, z, z}, v1[4] = {z, z, z, z};   // four independent chains: the FMA latency is exposed otherwise
@@ -169,7 +202,7 @@ __device__ __forceinline__ void cu3_pair_bwd(const Cu3& g, float2& p0, float2& p
   A.ql = __ffma2_rn(l1, swp(p1), A.ql);
   p1 = cmul(g.elr, g.eli, p1); l1 = cmul(g.elr, g.eli, l1);
 }
-template <int RT, int RC>
+template <int RT, int RC, int NA>
 __device__ __forceinline__ void cu3_loc(float2 (&st)[NA], const Cu3& g, bool post) {
 #pragma unroll
   for (int i = 0; i < NA / 4; ++i) {
@@ -181,7 +214,7 @@ __device__ __forceinline__ void cu3_loc(float2 (&st)[NA], const Cu3& g, bool pos
     for (int i = 0; i < NA / 4; ++i) { const int j1 = cpair_lo<RT, RC>(i) | (1 << RT); st[j1] = cmul(g.epr, g.epi, st[j1]); }
   }
 }
-template <int RB>
+template <int RB, int NA>
 __device__ __forceinline__ void cu3_all(float2 (&st)[NA], const Cu3& g, bool post) {
 #pragma unroll
   for (int i = 0; i < NA / 2; ++i) {
@@ -193,7 +226,7 @@ __device__ __forceinline__ void cu3_all(float2 (&st)[NA], const Cu3& g, bool pos
     for (int i = 0; i < NA / 2; ++i) { const int j1 = pair_lo<RB>(i) | (1 << RB); st[j1] = cmul(g.epr, g.epi, st[j1]); }
   }
 }
-template <int RT, int RC>
+template <int RT, int RC, int NA>
 __device__ __forceinline__ void cu3_loc_bwd(float2 (&ps)[NA], float2 (&ls)[NA], const Cu3& g, Cu3Acc& A, bool post) {
   if (post) {   // undo the inline post-phase first (g holds the conjugate phases)
 #pragma unroll
@@ -208,7 +241,7 @@ __device__ __forceinline__ void cu3_loc_bwd(float2 (&ps)[NA], float2 (&ls)[NA], 
     cu3_pair_bwd(g, ps[j0], ps[j1], ls[j0], ls[j1], A);
   }
 }
-template <int RB>
+template <int RB, int NA>
 __device__ __forceinline__ void cu3_all_bwd(float2 (&ps)[NA], float2 (&ls)[NA], const Cu3& g, Cu3Acc& A, bool post) {
   if (post) {
 #pragma unroll
@@ -226,6 +259,25 @@ __device__ __forceinline__ void cu3_all_bwd(float2 (&ps)[NA], float2 (&ls)[NA], 
 
 // ---- sums over the 32 register amplitudes: total and, per register bit r, the signed sum -------------
 // S[r] = sum_j (-1)^{j_r} v_j with a shared tree (61 packed adds); v_j are pairs, reduced per half.
+// KR < 5 (fewer amplitudes per thread): the same tree, written as a loop over the levels; S[r >= KR] stay unset.
+template <int KR, typename F>
+__device__ __forceinline__ void signed_sums2_small(F f, float2& total, float2 (&S)[kR]) {
+  constexpr int N = 1 << KR;
+  const float2 z = make_float2(0.f, 0.f);
+  float2 a[N], odd[KR];
+#pragma unroll
+  for (int i = 0; i < N; ++i) a[i] = f(i);
+#pragma unroll
+  for (int r = 0; r < KR; ++r) {
+    float2 o = z;
+#pragma unroll
+    for (int i = 0; i < (N >> (r + 1)); ++i) { o = __fadd2_rn(o, a[2 * i + 1]); a[i] = __fadd2_rn(a[2 * i], a[2 * i + 1]); }
+    odd[r] = o;
+  }
+  total = a[0];
+#pragma unroll
+  for (int r = 0; r < KR; ++r) S[r] = fma2(-2.f, odd[r], total);
+}
 template <typename F>
 __device__ __forceinline__ void signed_sums2(F f, float2& total, float2 (&S)[kR]) {
   const float2 z = make_float2(0.f, 0.f);
@@ -307,6 +359,7 @@ __device__ __forceinline__ float warp_sum4(float t0, float t1, float t2, float t
 // of the group that shares the buffer (a warp for n <= 10, 2^wb warps above).
 // buf: 0 when wa / ra already carry the (size-aligned) buffer address; else the buffer's shared address, added
 // after the XOR (cluster geometry: its two 64 KB buffers are not aligned to their size).
+template <int NA>
 __device__ __forceinline__ void smem_store_all(const float2 (&st)[NA], uint32_t buf, uint32_t wa, const uint32_t* woff) {
 #pragma unroll
   for (int q = 0; q < NA / 4; ++q) {
@@ -317,6 +370,7 @@ __device__ __forceinline__ void smem_store_all(const float2 (&st)[NA], uint32_t 
     sts64(buf + (wa ^ o.w), st[4 * q + 3].x, st[4 * q + 3].y);
   }
 }
+template <int NA>
 __device__ __forceinline__ void smem_load_all(float2 (&st)[NA], uint32_t buf, uint32_t ra, const uint32_t* roff) {
 #pragma unroll
   for (int q = 0; q < NA / 4; ++q) {
@@ -327,7 +381,7 @@ __device__ __forceinline__ void smem_load_all(float2 (&st)[NA], uint32_t buf, ui
     lds64(buf + (ra ^ o.w), st[4 * q + 3].x, st[4 * q + 3].y);
   }
 }
-template <typename Sync>
+template <typename Sync, int NA>
 __device__ __forceinline__ void exchange(float2 (&st)[NA], uint32_t buf, uint32_t wa, uint32_t ra, const uint32_t* woff,
                                          const uint32_t* roff, Sync sync) {
   sync();
@@ -345,6 +399,7 @@ __device__ __forceinline__ void st_cluster64(uint32_t local_addr, uint32_t rank,
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(rank));
   asm volatile("st.shared::cluster.v2.f32 [%0], {%1, %2};" ::"r"(remote), "f"(a), "f"(b) : "memory");
 }
+template <int NA>
 __device__ __forceinline__ void dsmem_store_all(const float2 (&st)[NA], uint32_t buf, uint32_t wa, const uint32_t* woff) {
 #pragma unroll
   for (int q = 0; q < NA / 4; ++q) {
@@ -363,7 +418,7 @@ __device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.w
 // sets alternate from one exchange to the next, so ONE cluster barrier per exchange suffices: a set is
 // written again only after every thread has passed the barrier of the exchange in between, i.e. after
 // all reads of it have completed.  TWO: psi and lam travel together (backward), sharing that barrier.
-template <bool TWO, typename Sync>
+template <bool TWO, typename Sync, int NA>
 __device__ __forceinline__ void exchange_global(float2 (&st)[NA], float2 (&st2)[NA], unsigned char* buf, unsigned char* buf2,
                                                 uint32_t wa, uint32_t ra, const uint32_t* woff, const uint32_t* roff, Sync sync) {
 #pragma unroll
@@ -399,7 +454,7 @@ __device__ __forceinline__ void exchange_global(float2 (&st)[NA], float2 (&st2)[
 
 // multiply by a diagonal (optionally its conjugate): big table [j][lane] or register-only table [j].
 // d*a = d.re * a + (-d.im, d.im) (.) swap(a); one table load serves psi and lam in the backward pass.
-template <bool CONJ, bool TWO>
+template <bool CONJ, bool TWO, int NA>
 __device__ __forceinline__ void diag_mul(float2 (&st)[NA], float2 (&st2)[NA], const float2* tbl, int stride, int lane_off) {
 #pragma unroll
   for (int j = 0; j < NA; ++j) {
@@ -452,8 +507,11 @@ struct Smem {
 //         per-thread bases and cross-CTA partial sums in global memory.
 // AMP: amplitude encoder (GEOM 0 only); a separate instantiation keeps its gather/scatter code and live
 // values out of the angle-encoder kernels.
-template <bool BWD, bool STATE, int GEOM, bool AMP>
-__global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
+// KR: register bits (2^KR amplitudes per thread).  5 is the throughput geometry; 3 and 4 spread a batch over four / two
+// times as many warps (a warp then carries 256 / 512 amplitudes): lower latency for small batches, less state per thread.
+template <bool BWD, bool STATE, int GEOM, bool AMP, int KR = 5>
+__global__ void __launch_bounds__(BWD ? 256 : 512, (BWD && KR < 5) ? 2 : 1) k_vm(const VmArgs a) {
+  constexpr int NA = 1 << KR;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   // GEOM 0 always runs with the full CTA (compile-time constants); the others may be launched with fewer warps
@@ -482,7 +540,7 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
     const uint32_t s0 = (uint32_t)__cvta_generic_to_shared(smem_raw);
     // cluster geometry: two CTA-wide 64 KB buffers right behind the tables (addressed as base + offset, so they
     // need no alignment to their size); otherwise one buffer per group at the next multiple of its size
-    const uint32_t gbuf = CL ? 65536u : (8192u << wbits);
+    const uint32_t gbuf = CL ? 65536u : ((256u * NA) << wbits);
     const uint32_t xb = CL ? ((s0 + a.table_bytes + 15u) & ~15u) : ((s0 + a.table_bytes + gbuf - 1u) & ~(gbuf - 1u));
     S.xbuf = xb + (uint32_t)grp * gbuf;
     unsigned char* const p = smem_raw;
@@ -505,21 +563,75 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
     }
     const int tid = threadIdx.x;
     const uint32_t* src; uint32_t* dst; int words;
-    for (int i = tid; i < a.n_ops; i += blockDim.x) {
-      const MicroOp m = a.ops[i];
-      SOp o;
-      o.h = m.pad0 | ((m.b & kCu3InlinePost) ? kPostBit : 0); o.idx = m.idx; o.acc = m.acc; o.aux = m.aux;
-      o.cf = *reinterpret_cast<const float4*>(a.coef + (size_t)m.pad1 * QNN_COEF_STRIDE);
-      S.ops[i] = o;
+    bool inl = false;
+    if constexpr (KR < 5) inl = a.inline_prep != 0;
+    if (!inl) {
+      for (int i = tid; i < a.n_ops; i += blockDim.x) {
+        const MicroOp m = a.ops[i];
+        SOp o;
+        o.h = m.pad0 | ((m.b & kCu3InlinePost) ? kPostBit : 0); o.idx = m.idx; o.acc = m.acc; o.aux = m.aux;
+        o.cf = *reinterpret_cast<const float4*>(a.coef + (size_t)m.pad1 * QNN_COEF_STRIDE);
+        S.ops[i] = o;
+      }
     }
     src = reinterpret_cast<const uint32_t*>(a.exchanges); dst = reinterpret_cast<uint32_t*>(S.exchanges); words = a.n_exchanges * (int)(sizeof(Exchange) / 4);
     for (int i = tid; i < words; i += blockDim.x) dst[i] = src[i];
     if (!MW) for (int i = tid; i < a.n_xbase; i += blockDim.x) S.xbase[i] = a.xbase[i];
     src = reinterpret_cast<const uint32_t*>(a.diags); dst = reinterpret_cast<uint32_t*>(S.diags); words = a.n_diags * (int)(sizeof(DiagDesc) / 4);
     for (int i = tid; i < words; i += blockDim.x) dst[i] = src[i];
-    for (int i = tid; i < a.n_coef * 8; i += blockDim.x) S.coef[i] = a.coef[(size_t)(i >> 3) * QNN_COEF_STRIDE + (i & 7)];
-    if (wbits == 0) for (int i = tid; i < a.n_big * 32 * G; i += blockDim.x) sbig[i] = a.big[i];
-    for (int i = tid; i < a.n_small * 32; i += blockDim.x) S.small[i] = a.small[i];
+    if constexpr (KR < 5) {
+      if (inl) {   // (host: only for wbits == 0, where every table lives in shared memory)
+        // every term's angle and bit masks once, staged in the (not yet used) exchange-buffer area: the table
+        // entries below then read shared memory instead of chasing terms[] and w[] through L2 per entry
+        struct STerm { double phi; unsigned m0, m1; };
+        STerm* const st = reinterpret_cast<STerm*>(smem_raw + (((size_t)a.table_bytes + 15) & ~(size_t)15));
+        const int nst = min(a.n_terms, 128);     // 2 KB: fits the smallest buffer area (16 warps x 2 KB)
+        for (int i = tid; i < nst; i += blockDim.x) {
+          const DiagTerm tm = a.terms[i];
+          const double v = (tm.src == QNN_SRC_CONST) ? (double)tm.value : (double)a.w[tm.src];
+          st[i].phi = tm.kind == 0 ? 0.5 * v : (tm.kind == 1 ? 3.14159265358979323846 : v);
+          st[i].m0 = 1u << tm.bit0;
+          st[i].m1 = tm.kind == 0 ? 0u : (1u << tm.bit1);
+        }
+        for (int i = tid; i < a.n_coef; i += blockDim.x) make_coef_row(a.coef_ops[i], a.w, S.coef + i * 8);
+        __syncthreads();
+        const unsigned tmask = (1u << tb) - 1u;
+        for (int d = 0; d < a.n_diags; ++d) {
+          const DiagDesc D = a.diags[d];
+          const int entries = D.is_reg ? NA : NA * G;
+          for (int e = tid; e < entries; e += blockDim.x) {
+            const int j = D.is_reg ? e : (e / G), t = D.is_reg ? 0 : (e % G);
+            const unsigned p = (unsigned)j | (((unsigned)t & tmask) << KR);
+            double ang = 0.0;
+            if (D.first_term + D.n_terms <= nst) {
+              for (int k = D.first_term; k < D.first_term + D.n_terms; ++k) {
+                if (st[k].m1 == 0u) ang += (p & st[k].m0) ? st[k].phi : -st[k].phi;
+                else if ((p & st[k].m0) && (p & st[k].m1)) ang += st[k].phi;
+              }
+            } else {
+              ang = diag_angle(D, a.terms, a.w, p);
+            }
+            double sn, cs;
+            sincos(ang, &sn, &cs);
+            const float2 v = make_float2((float)cs, (float)sn);
+            if (D.is_reg) S.small[(size_t)D.table * NA + e] = v; else sbig[(size_t)D.table * NA * G + e] = v;
+          }
+        }
+        __syncthreads();
+        for (int i = tid; i < a.n_ops; i += blockDim.x) {
+          const MicroOp m = a.ops[i];
+          SOp o;
+          o.h = m.pad0 | ((m.b & kCu3InlinePost) ? kPostBit : 0); o.idx = m.idx; o.acc = m.acc; o.aux = m.aux;
+          o.cf = *reinterpret_cast<const float4*>(S.coef + (size_t)m.pad1 * 8);
+          S.ops[i] = o;
+        }
+      }
+    }
+    if (!inl) {
+      for (int i = tid; i < a.n_coef * 8; i += blockDim.x) S.coef[i] = a.coef[(size_t)(i >> 3) * QNN_COEF_STRIDE + (i & 7)];
+      if (wbits == 0) for (int i = tid; i < a.n_big * NA * G; i += blockDim.x) sbig[i] = a.big[i];
+      for (int i = tid; i < a.n_small * NA; i += blockDim.x) S.small[i] = a.small[i];
+    }
     if (BWD) {
       for (int i = tid; i < WARPS * max(a.n_acc, 1); i += blockDim.x) S.wacc[i] = 0.f;
       for (int i = tid; i < WARPS * spw * max(a.n_angle, 1); i += blockDim.x) S.gxacc[i] = 0.f;
@@ -548,7 +660,7 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
   const int n_ang = a.n_angle;
   // amplitude encoder: logical index (wire 0 = most significant bit) of this thread's register j is klog_t | klog_j(j)
   auto klog = [&](unsigned p) { unsigned k = 0; for (int w = 0; w < a.n; ++w) k |= ((p >> a.init_bit_of_wire[w]) & 1u) << (a.n - 1 - w); return k; };
-  const unsigned klog_t = (AMP) ? klog((unsigned)tis << kR) : 0u;
+  const unsigned klog_t = (AMP) ? klog((unsigned)tis << KR) : 0u;
   float2 ps[NA];
   const long long n_batches = (a.B + spw - 1) / spw;
   for (long long wb = CL ? (long long)cid : (long long)blockIdx.x * groups + grp; wb < n_batches;
@@ -611,44 +723,44 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
         // merged diagonal after a controlled U3 executed twice per warp).
         __syncwarp();
         switch (op.h & 255) {
-#define H_CASE_ROT(RB) case H_ROT + RB: rot<RB>(ps, cfa.x, cfa.y); break;
+#define H_CASE_ROT(RB) case H_ROT + RB: if constexpr (RB < KR) rot<RB>(ps, cfa.x, cfa.y); break;
           H_CASE_ROT(0) H_CASE_ROT(1) H_CASE_ROT(2) H_CASE_ROT(3) H_CASE_ROT(4)
 #undef H_CASE_ROT
-#define H_CASE_ROTX(RB) case H_ROTX + RB: { const float2 ab = xc[op.idx]; rot<RB>(ps, ab.x, ab.y); } break;
+#define H_CASE_ROTX(RB) case H_ROTX + RB: if constexpr (RB < KR) { const float2 ab = xc[op.idx]; rot<RB>(ps, ab.x, ab.y); } break;
           H_CASE_ROTX(0) H_CASE_ROTX(1) H_CASE_ROTX(2) H_CASE_ROTX(3) H_CASE_ROTX(4)
 #undef H_CASE_ROTX
-#define H_CASE_CU3L(RT, RC) case H_CU3L + RT * 4 + (RC < RT ? RC : RC - 1): { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_loc<RT, RC>(ps, g, op.h & kPostBit); } break;
+#define H_CASE_CU3L(RT, RC) case H_CU3L + RT * 4 + (RC < RT ? RC : RC - 1): if constexpr (RT < KR && RC < KR) { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_loc<RT, RC>(ps, g, op.h & kPostBit); } break;
           H_CASE_CU3L(0, 1) H_CASE_CU3L(0, 2) H_CASE_CU3L(0, 3) H_CASE_CU3L(0, 4)
           H_CASE_CU3L(1, 0) H_CASE_CU3L(1, 2) H_CASE_CU3L(1, 3) H_CASE_CU3L(1, 4)
           H_CASE_CU3L(2, 0) H_CASE_CU3L(2, 1) H_CASE_CU3L(2, 3) H_CASE_CU3L(2, 4)
           H_CASE_CU3L(3, 0) H_CASE_CU3L(3, 1) H_CASE_CU3L(3, 2) H_CASE_CU3L(3, 4)
           H_CASE_CU3L(4, 0) H_CASE_CU3L(4, 1) H_CASE_CU3L(4, 2) H_CASE_CU3L(4, 3)
 #undef H_CASE_CU3L
-#define H_CASE_CU3P(RB) case H_CU3P + RB: if (__popc(tis & op.aux) & 1) { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_all<RB>(ps, g, op.h & kPostBit); } break;
+#define H_CASE_CU3P(RB) case H_CU3P + RB: if constexpr (RB < KR) { if (__popc(tis & op.aux) & 1) { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_all<RB>(ps, g, op.h & kPostBit); } } break;
           H_CASE_CU3P(0) H_CASE_CU3P(1) H_CASE_CU3P(2) H_CASE_CU3P(3) H_CASE_CU3P(4)
 #undef H_CASE_CU3P
-          case H_ROT5: {
+#define ROT_BIT(K) if constexpr (K < KR) rot<K>(ps, ab[K].x, ab[K].y);
+          case H_ROT5: {   // rotations on all KR register bits
             float2 ab[5];
 #pragma unroll
-            for (int k = 0; k < 5; ++k) ab[k] = *reinterpret_cast<const float2*>(S.coef + (op.idx + ((op.aux >> (3 * k)) & 7)) * 8);
-            rot<0>(ps, ab[0].x, ab[0].y); rot<1>(ps, ab[1].x, ab[1].y); rot<2>(ps, ab[2].x, ab[2].y);
-            rot<3>(ps, ab[3].x, ab[3].y); rot<4>(ps, ab[4].x, ab[4].y);
+            for (int k = 0; k < KR; ++k) ab[k] = *reinterpret_cast<const float2*>(S.coef + (op.idx + ((op.aux >> (3 * k)) & 7)) * 8);
+            ROT_BIT(0) ROT_BIT(1) ROT_BIT(2) ROT_BIT(3) ROT_BIT(4)
           } break;
           case H_ROTX5: {
             float2 ab[5];
 #pragma unroll
-            for (int k = 0; k < 5; ++k) ab[k] = xc[(op.idx >> (5 * k)) & 31];
-            rot<0>(ps, ab[0].x, ab[0].y); rot<1>(ps, ab[1].x, ab[1].y); rot<2>(ps, ab[2].x, ab[2].y);
-            rot<3>(ps, ab[3].x, ab[3].y); rot<4>(ps, ab[4].x, ab[4].y);
+            for (int k = 0; k < KR; ++k) ab[k] = xc[(op.idx >> (5 * k)) & 31];
+            ROT_BIT(0) ROT_BIT(1) ROT_BIT(2) ROT_BIT(3) ROT_BIT(4)
           } break;
-          case H_CHAIN: {
+#undef ROT_BIT
+          case H_CHAIN: {   // controlled U3 (target, control) = (1,0), (2,1), ... up to the last register bit
             { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), false); cu3_loc<1, 0>(ps, g, op.aux & 1); }
             { const Cu3 g = load_cu3(S.coef + (op.idx + 1) * 8, false); cu3_loc<2, 1>(ps, g, op.aux & 2); }
-            { const Cu3 g = load_cu3(S.coef + (op.idx + 2) * 8, false); cu3_loc<3, 2>(ps, g, op.aux & 4); }
-            { const Cu3 g = load_cu3(S.coef + (op.idx + 3) * 8, false); cu3_loc<4, 3>(ps, g, op.aux & 8); }
+            if constexpr (KR > 3) { const Cu3 g = load_cu3(S.coef + (op.idx + 2) * 8, false); cu3_loc<3, 2>(ps, g, op.aux & 4); }
+            if constexpr (KR > 4) { const Cu3 g = load_cu3(S.coef + (op.idx + 3) * 8, false); cu3_loc<4, 3>(ps, g, op.aux & 8); }
           } break;
-          case H_DIAG: diag_mul<false, false>(ps, ps, S.big + (size_t)op.idx * 32 * G, G, tig); break;
-          case H_DIAGR: diag_mul<false, false>(ps, ps, S.small + op.idx * 32, 1, 0); break;
+          case H_DIAG: diag_mul<false, false>(ps, ps, S.big + (size_t)op.idx * NA * G, G, tig); break;
+          case H_DIAGR: diag_mul<false, false>(ps, ps, S.small + op.idx * NA, 1, 0); break;
           case H_XCHG: {
             const Exchange* X = S.exchanges + op.idx;
             if constexpr (CL) {
@@ -688,20 +800,25 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
     if constexpr (!BWD) {
       // ================= measurement: <Z> per physical bit =================
       float2 tot2, S2[kR];
-      signed_sums2([&](int j) { return __fmul2_rn(ps[j], ps[j]); }, tot2, S2);
+      if constexpr (KR == 5) signed_sums2([&](int j) { return __fmul2_rn(ps[j], ps[j]); }, tot2, S2);
+      else signed_sums2_small<KR>([&](int j) { return __fmul2_rn(ps[j], ps[j]); }, tot2, S2);
       const float tot = tot2.x + tot2.y;
-      // per-warp partials: [0..4] register bits, [5..9] lane bits, [10] plain total (for the warp bits)
+      // per-warp partials, indexed by physical bit: [0, KR) register bits, [KR, KR + 5) lane bits, [10] plain total
+      // (for the warp bits)
+      constexpr int PW = KR + 5;   // first warp bit
       float val[11];
 #pragma unroll
-      for (int r = 0; r < kR; ++r) val[r] = sample_sum(S2[r].x + S2[r].y, lbits);
+      for (int r = 0; r < KR; ++r) val[r] = sample_sum(S2[r].x + S2[r].y, lbits);
 #pragma unroll
-      for (int b = 0; b < 5; ++b) val[kR + b] = (b < lbits) ? sample_sum(((lane >> b) & 1) ? -tot : tot, lbits) : 0.f;
+      for (int b = 0; b < 5; ++b) val[KR + b] = (b < lbits) ? sample_sum(((lane >> b) & 1) ? -tot : tot, lbits) : 0.f;
+#pragma unroll
+      for (int c = PW; c < 10; ++c) val[c] = 0.f;
       val[10] = sample_sum(tot, lbits);
       if (wbits == 0) {
         if (active && tis == 0) {
           float* yrow = a.y + (size_t)bs * a.n;
 #pragma unroll
-          for (int pb = 0; pb < 10; ++pb)
+          for (int pb = 0; pb < PW; ++pb)
             if (pb < a.n) yrow[a.wire_of_bit[pb]] = val[pb];
         }
       } else {
@@ -718,8 +835,8 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
           const int stride = CL ? 48 : 16;
           float t = 0.f;
           for (int w = 0; w < gwarps; ++w) {
-            const float v = CL ? __ldcg(r0 + w * stride + (lane < 10 ? lane : 10)) : r0[w * stride + (lane < 10 ? lane : 10)];
-            t += (lane >= 10 && ((w >> (lane - 10)) & 1)) ? -v : v;
+            const float v = CL ? __ldcg(r0 + w * stride + (lane < PW ? lane : 10)) : r0[w * stride + (lane < PW ? lane : 10)];
+            t += (lane >= PW && ((w >> (lane - PW)) & 1)) ? -v : v;
           }
           a.y[(size_t)bs * a.n + a.wire_of_bit[lane]] = t;
         }
@@ -728,15 +845,17 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
       // ================= seed lam = (sum_q gy_q Z_q) psi =================
       float2 ls[NA];
       {
-        float g[kR + kMaxThreadBits];
+        float g[KR + kMaxThreadBits];
         const float* gyrow = a.gy + (size_t)(active ? bs : 0) * a.n;
 #pragma unroll
-        for (int pb = 0; pb < kR + kMaxThreadBits; ++pb) g[pb] = (active && pb < a.n) ? gyrow[a.wire_of_bit[pb]] : 0.f;
+        for (int pb = 0; pb < KR + kMaxThreadBits; ++pb) g[pb] = (active && pb < a.n) ? gyrow[a.wire_of_bit[pb]] : 0.f;
         float cl = 0.f;
 #pragma unroll
-        for (int b = 0; b < kMaxThreadBits; ++b) cl += ((tis >> b) & 1) ? -g[kR + b] : g[kR + b];
+        for (int b = 0; b < kMaxThreadBits; ++b) cl += ((tis >> b) & 1) ? -g[KR + b] : g[KR + b];
         float cj[NA];
-        cj[0] = cl + g[0] + g[1] + g[2] + g[3] + g[4];
+        cj[0] = cl;
+#pragma unroll
+        for (int r = 0; r < KR; ++r) cj[0] += g[r];
 #pragma unroll
         for (int j = 1; j < NA; ++j) {
           const int low = j & (-j);                      // lowest set bit
@@ -757,11 +876,11 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
         // merged diagonal after a controlled U3 executed twice per warp).
         __syncwarp();
         switch (op.h & 255) {
-#define H_CASE_ROT(RB) case H_ROT + RB: { float v = rot_grad<RB>(ps, ls); rot<RB>(ps, -cfa.x, -cfa.y); rot<RB>(ls, -cfa.x, -cfa.y); \
+#define H_CASE_ROT(RB) case H_ROT + RB: if constexpr (RB < KR) { float v = rot_grad<RB>(ps, ls); rot<RB>(ps, -cfa.x, -cfa.y); rot<RB>(ls, -cfa.x, -cfa.y); \
             if (op.acc >= 0) { v = warp_sum(v); if (lane == 0) wacc[op.acc] += v; } } break;
           H_CASE_ROT(0) H_CASE_ROT(1) H_CASE_ROT(2) H_CASE_ROT(3) H_CASE_ROT(4)
 #undef H_CASE_ROT
-#define H_CASE_ROTX(RB) case H_ROTX + RB: { const float2 ab = xc[op.idx]; float v = rot_grad<RB>(ps, ls); rot<RB>(ps, -ab.x, -ab.y); rot<RB>(ls, -ab.x, -ab.y); \
+#define H_CASE_ROTX(RB) case H_ROTX + RB: if constexpr (RB < KR) { const float2 ab = xc[op.idx]; float v = rot_grad<RB>(ps, ls); rot<RB>(ps, -ab.x, -ab.y); rot<RB>(ls, -ab.x, -ab.y); \
             v = sample_sum(v, lbits); if ((lane & ((1 << lbits) - 1)) == 0) gxacc[siw * n_ang + op.idx] += v; } break;
           H_CASE_ROTX(0) H_CASE_ROTX(1) H_CASE_ROTX(2) H_CASE_ROTX(3) H_CASE_ROTX(4)
 #undef H_CASE_ROTX
@@ -771,7 +890,7 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
                                         -2.f * (A.ql.x - A.ql.y), 0.f, lane);                               \
               if ((lane & 7) == 0 && (lane >> 3) < 3) wacc[(ACC) + (lane >> 3)] += r;                       \
             }
-#define H_CASE_CU3L(RT, RC) case H_CU3L + RT * 4 + (RC < RT ? RC : RC - 1): { const float2 z = make_float2(0.f, 0.f); Cu3Acc A{z, z, z, z}; \
+#define H_CASE_CU3L(RT, RC) case H_CU3L + RT * 4 + (RC < RT ? RC : RC - 1): if constexpr (RT < KR && RC < KR) { const float2 z = make_float2(0.f, 0.f); Cu3Acc A{z, z, z, z}; \
             const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), true); cu3_loc_bwd<RT, RC>(ps, ls, g, A, op.h & kPostBit); CU3_REDUCE(A, op.acc) } break;
           H_CASE_CU3L(0, 1) H_CASE_CU3L(0, 2) H_CASE_CU3L(0, 3) H_CASE_CU3L(0, 4)
           H_CASE_CU3L(1, 0) H_CASE_CU3L(1, 2) H_CASE_CU3L(1, 3) H_CASE_CU3L(1, 4)
@@ -779,15 +898,15 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
           H_CASE_CU3L(3, 0) H_CASE_CU3L(3, 1) H_CASE_CU3L(3, 2) H_CASE_CU3L(3, 4)
           H_CASE_CU3L(4, 0) H_CASE_CU3L(4, 1) H_CASE_CU3L(4, 2) H_CASE_CU3L(4, 3)
 #undef H_CASE_CU3L
-#define H_CASE_CU3P(RB) case H_CU3P + RB: { const float2 z = make_float2(0.f, 0.f); Cu3Acc A{z, z, z, z}; \
+#define H_CASE_CU3P(RB) case H_CU3P + RB: if constexpr (RB < KR) { const float2 z = make_float2(0.f, 0.f); Cu3Acc A{z, z, z, z}; \
             if (__popc(tis & op.aux) & 1) { const Cu3 g = make_cu3(cfa, *reinterpret_cast<const float4*>(S.coef + op.idx * 8 + 4), true); cu3_all_bwd<RB>(ps, ls, g, A, op.h & kPostBit); } \
             CU3_REDUCE(A, op.acc) } break;
           H_CASE_CU3P(0) H_CASE_CU3P(1) H_CASE_CU3P(2) H_CASE_CU3P(3) H_CASE_CU3P(4)
 #undef H_CASE_CU3P
           case H_ROT5: {
-            float v[5];
+            float v[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
 #define ROT5_STEP(K)                                                                                       \
-            {                                                                                              \
+            if constexpr (K < KR) {                                                                        \
               const int pos = (op.aux >> (3 * K)) & 7;                                                     \
               const float2 ab = *reinterpret_cast<const float2*>(S.coef + (op.idx + pos) * 8);             \
               v[K] = rot_grad<K>(ps, ls);                                                                  \
@@ -798,11 +917,11 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
             // five sums in one halving butterfly: lane 8k' ... holds component (lane >> 2)
             const float t8[16] = {v[0], v[1], v[2], v[3], v[4], 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
             const float r = warp_sum16(t8, lane);
-            if ((lane & 1) == 0 && (lane >> 1) < 5) wacc[op.acc + ((op.aux >> (3 * (lane >> 1))) & 7)] += r;
+            if ((lane & 1) == 0 && (lane >> 1) < KR) wacc[op.acc + ((op.aux >> (3 * (lane >> 1))) & 7)] += r;
           } break;
           case H_ROTX5: {
 #define ROTX5_STEP(K)                                                                                      \
-            {                                                                                              \
+            if constexpr (K < KR) {                                                                        \
               const int col = (op.idx >> (5 * K)) & 31;                                                    \
               const float2 ab = xc[col];                                                                   \
               float v = rot_grad<K>(ps, ls);                                                               \
@@ -815,7 +934,7 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
           } break;
           case H_CHAIN: {
 #define CHAIN_STEP(K, RT, RC)                                                                              \
-            {                                                                                              \
+            if constexpr (RT < KR) {                                                                       \
               const float2 z = make_float2(0.f, 0.f);                                                      \
               Cu3Acc A{z, z, z, z};                                                                        \
               const Cu3 g = load_cu3(S.coef + (op.idx + K) * 8, true);                                     \
@@ -834,26 +953,27 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, 1) k_vm(const VmArgs a) {
             const DiagDesc* D = S.diags + op.aux;
             float2 tot2, S2[kR];
             // Im(conj(lam) psi) = lam.re psi.im - lam.im psi.re, kept as the pair (lam.re psi.im, lam.im psi.re)
-            signed_sums2([&](int j) { return __fmul2_rn(ls[j], swp(ps[j])); }, tot2, S2);
+            if constexpr (KR == 5) signed_sums2([&](int j) { return __fmul2_rn(ls[j], swp(ps[j])); }, tot2, S2);
+            else signed_sums2_small<KR>([&](int j) { return __fmul2_rn(ls[j], swp(ps[j])); }, tot2, S2);
             const float tot = tot2.x - tot2.y;
             // all (up to ten) per-bit sums in one halving butterfly; lane l ends up with component l >> 1
             float t16[16];
 #pragma unroll
-            for (int r = 0; r < kR; ++r) t16[r] = S2[r].x - S2[r].y;
+            for (int r = 0; r < KR; ++r) t16[r] = S2[r].x - S2[r].y;
 #pragma unroll
-            for (int b = 0; b < kMaxThreadBits; ++b) t16[kR + b] = ((tis >> b) & 1) ? -tot : tot;
+            for (int b = 0; b < kMaxThreadBits; ++b) t16[KR + b] = ((tis >> b) & 1) ? -tot : tot;
 #pragma unroll
-            for (int k = kR + kMaxThreadBits; k < 16; ++k) t16[k] = 0.f;
+            for (int k = KR + kMaxThreadBits; k < 16; ++k) t16[k] = 0.f;
             const float r = warp_sum16(t16, lane);
             if ((lane & 1) == 0) {
               const int comp = lane >> 1;
-              const int ai = comp < kR ? D->acc_reg[comp]
-                                       : (comp < kR + kMaxThreadBits && (op.h & 255) == H_DIAG ? D->acc_thr[comp - kR] : -1);
+              const int ai = comp < KR ? D->acc_reg[comp]
+                                       : (comp < KR + kMaxThreadBits && (op.h & 255) == H_DIAG ? D->acc_thr[comp - KR] : -1);
               if (ai >= 0) wacc[ai] += r;
             }
             __syncwarp();   // reconverge before the table multiply (ptxas otherwise runs it once per lane subset)
-            if ((op.h & 255) == H_DIAG) diag_mul<true, true>(ps, ls, S.big + (size_t)op.idx * 32 * G, G, tig);
-            else diag_mul<true, true>(ps, ls, S.small + op.idx * 32, 1, 0);
+            if ((op.h & 255) == H_DIAG) diag_mul<true, true>(ps, ls, S.big + (size_t)op.idx * NA * G, G, tig);
+            else diag_mul<true, true>(ps, ls, S.small + op.idx * NA, 1, 0);
           } break;
           case H_XCHG: {   // inverse: roles of the two address sets swapped
             const Exchange* X = S.exchanges + op.idx;
@@ -971,14 +1091,17 @@ int launch_kernel(K kern, const LaunchCfg& lc, const VmArgs& a) {
   return QNN_OK;
 }
 
-template <int GEOM, bool AMP>
+template <int GEOM, bool AMP, int KR = 5>
 int launch_geom(bool bwd, bool state, const LaunchCfg& lc, const VmArgs& a) {
-  if (bwd) return state ? launch_kernel(k_vm<true, true, GEOM, AMP>, lc, a) : launch_kernel(k_vm<true, false, GEOM, AMP>, lc, a);
-  return state ? launch_kernel(k_vm<false, true, GEOM, AMP>, lc, a) : launch_kernel(k_vm<false, false, GEOM, AMP>, lc, a);
+  if (bwd) return state ? launch_kernel(k_vm<true, true, GEOM, AMP, KR>, lc, a) : launch_kernel(k_vm<true, false, GEOM, AMP, KR>, lc, a);
+  return state ? launch_kernel(k_vm<false, true, GEOM, AMP, KR>, lc, a) : launch_kernel(k_vm<false, false, GEOM, AMP, KR>, lc, a);
 }
 
 // one translation unit per geometry (compiled in parallel): qnn_vm_g0.cu, qnn_vm_g0a.cu, qnn_vm_g1.cu, qnn_vm_g2.cu
 int launch_g0(bool bwd, bool state, const LaunchCfg& lc, const VmArgs& a);    // n <= 10, angle inputs
+int launch_g0_k3(bool bwd, bool state, const LaunchCfg& lc, const VmArgs& a);  // n <= 8, 8 amplitudes per thread
+int launch_g0_k4(bool bwd, bool state, const LaunchCfg& lc, const VmArgs& a);  // n <= 9, 16 amplitudes per thread
+int launch_g1_k4(bool bwd, bool state, const LaunchCfg& lc, const VmArgs& a);  // n = 10..12, 16 amplitudes per thread
 int launch_g0a(bool bwd, bool state, const LaunchCfg& lc, const VmArgs& a);   // n <= 10, amplitude encoder
 int launch_g1(bool bwd, bool state, const LaunchCfg& lc, const VmArgs& a);    // n = 11..13
 int launch_g2(bool bwd, bool state, const LaunchCfg& lc, const VmArgs& a);    // n = 14..16 (clusters)

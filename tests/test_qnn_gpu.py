@@ -245,7 +245,7 @@ def test_kernel_family_selection_and_both_families_agree():
     for make in (lambda: qris_b200.reference_circuit(6, 3), lambda: qris_b200.u3cu3_circuit(10, 2),
                  lambda: qris_b200.u3cu3_circuit(7, 2), lambda: qris_b200.reference_circuit(9, 2)):
         fast = make()
-        assert _plan(fast, 64) == "vm-register"
+        assert _plan(fast, 64).startswith("vm-register")
         slow = make().generic()
         assert _plan(slow, 64).startswith("generic")
         x, w, gy = seeded_inputs(fast, 77, seed=5)
@@ -253,7 +253,8 @@ def test_kernel_family_selection_and_both_families_agree():
         for u, v, name in zip(a, b, ("y", "gx", "gw")):
             assert_close(u, v, rel=2e-5, scale=float(np.abs(v).max()), what=name)
         check_against_oracle(slow, 33, seed=1)
-    assert _plan(qris_b200.reference_circuit(4, 1), 8).startswith("generic")
+    assert _plan(qris_b200.reference_circuit(2, 1), 8).startswith("generic")
+    assert _plan(qris_b200.reference_circuit(4, 1), 8) == "vm-register-narrow"      # 3 and 4 qubits: narrow variant only
     assert _plan(qris_b200.reference_circuit(12, 1), 8) == "vm-register"
     assert _plan(qris_b200.reference_circuit(14, 1), 8) == "vm-register"
 
@@ -262,8 +263,53 @@ def test_kernel_family_selection_and_both_families_agree():
 @pytest.mark.parametrize("B", [1, 3, 32, 1000])
 def test_vm_all_widths_and_ragged_batches(n, B):
     """Every lane/sample geometry of the VM (2^(n-5) lanes per sample), including partially filled warps."""
-    check_against_oracle(qris_b200.reference_circuit(n, 2), B, seed=n * 7 + B)
-    check_against_oracle(qris_b200.u3cu3_circuit(n, 1), B, seed=n * 11 + B)
+    check_against_oracle(qris_b200.reference_circuit(n, 2).pinned("wide"), B, seed=n * 7 + B)
+    check_against_oracle(qris_b200.u3cu3_circuit(n, 1).pinned("wide"), B, seed=n * 11 + B)
+
+
+@pytest.mark.parametrize("n", [3, 4, 5, 6, 7, 8])
+@pytest.mark.parametrize("B", [1, 3, 256, 4096])
+def test_narrow_variant_parity(n, B):
+    """8 amplitudes per thread (a warp carries 256): the variant small batches run on, at the reference's own
+    sizes (n = 6, B = 256 per call, Run:341-352; B = 4096 is BASELINE configs[1]) and for 3 and 4 qubits, which
+    only this variant takes.  Plain pair and saved-state pair against the oracle."""
+    for circ in (qris_b200.reference_circuit(n, 3).pinned("narrow"), qris_b200.u3cu3_circuit(n, 2).pinned("narrow")):
+        assert _plan(circ, B) == "vm-register-narrow"
+        check_against_oracle(circ, B, seed=n * 13 + B)
+        x, w, gy = (t.cuda() for t in seeded_inputs(circ, B, seed=n + B))
+        y1, state = qris_b200.qnn_forward_raw(circ, x, w, save_state=True)
+        gx0, gw0 = qris_b200.qnn_backward_raw(circ, x, w, gy)
+        gx1, gw1 = qris_b200.qnn_backward_raw(circ, x, w, gy, state=state)
+        assert state is not None and torch.equal(y1, qris_b200.qnn_forward_raw(circ, x, w))
+        assert_close(gx1.cpu().numpy(), gx0.cpu().numpy(), scale=float(gx0.abs().max()), what="gx saved vs recompute")
+        assert_close(gw1.cpu().numpy(), gw0.cpu().numpy(), scale=float(gw0.abs().max()), what="gw saved vs recompute")
+
+
+def test_variant_is_chosen_by_batch_size_and_variants_agree():
+    """Unpinned circuits of up to 8 qubits pick the narrow variant for batches that would leave warp slots of the
+    wide one empty, the wide one for large batches; both give the same numbers."""
+    circ = qris_b200.reference_circuit(6, 3)
+    assert _plan(circ, 256) == "vm-register-narrow" and _plan(circ, 4096) == "vm-register-narrow"
+    assert _plan(circ, 65536) == "vm-register"
+    assert _plan(qris_b200.reference_circuit(10, 3), 256) == "vm-register"          # no narrow variant above 8 qubits
+    x, w, gy = seeded_inputs(circ, 1000, seed=3)
+    a, b = run_gpu(circ.pinned("wide"), x, w, gy), run_gpu(circ.pinned("narrow"), x, w, gy)
+    for u, v, name in zip(a, b, ("y", "gx", "gw")):
+        assert_close(u, v, rel=2e-5, scale=float(np.abs(v).max()), what=name)
+
+
+@pytest.mark.parametrize("n,B", [(5, 70), (8, 33), (9, 5), (10, 1), (10, 37), (11, 6), (12, 3)])
+def test_sixteen_amplitudes_per_thread_variant(n, B):
+    """The occupancy experiment (QNN_CREATE_16_PER_THREAD): half the state per thread, twice the warps; n = 10 then
+    spans two warps per sample.  Same results as the oracle."""
+    for circ in (qris_b200.u3cu3_circuit(n, 2).pinned("16-per-thread"), qris_b200.reference_circuit(n, 2).pinned("16-per-thread")):
+        assert _plan(circ, B) == "vm-register-16"
+        check_against_oracle(circ, B, seed=n * 5 + B)
+        x, w, gy = (t.cuda() for t in seeded_inputs(circ, B, seed=n))
+        _, state = qris_b200.qnn_forward_raw(circ, x, w, save_state=True)
+        gx0, gw0 = qris_b200.qnn_backward_raw(circ, x, w, gy)
+        gx1, gw1 = qris_b200.qnn_backward_raw(circ, x, w, gy, state=state)
+        assert_close(gw1.cpu().numpy(), gw0.cpu().numpy(), scale=float(gw0.abs().max()), what="gw saved vs recompute")
 
 
 @pytest.mark.parametrize("n", [11, 12, 13])
@@ -285,12 +331,14 @@ def test_vm_irregular_circuit():
             Op("CZ", (3, 4)), Op("RZ", (4,), (("c", 1.3),)), Op("CNOT", (4, 0)), Op("CNOT", (0, 4)), Op("RY", (0,), (("w", 8),)),
             Op("RX", (2,), (("w", 2),)), Op("CU3", (0, 1), (("c", 0.2), ("w", 6), ("c", -0.7)))]
     circ = qris_b200.Circuit(n, ops, n_inputs=n, n_weights=9)
-    assert _plan(circ, 10) == "vm-register"
-    check_against_oracle(circ, 45, seed=2)
+    assert _plan(circ, 10).startswith("vm-register")
+    for variant in ("wide", "narrow", "16-per-thread"):
+        check_against_oracle(circ.pinned(variant), 45, seed=2)
 
 
 @pytest.mark.parametrize("make,B", [(lambda: qris_b200.u3cu3_circuit(10, 2), 100), (lambda: qris_b200.reference_circuit(6, 3), 300),
-                                     (lambda: qris_b200.reference_circuit(7, 2), 33), (lambda: qris_b200.reference_circuit(4, 2), 20)])
+                                     (lambda: qris_b200.reference_circuit(7, 2), 33), (lambda: qris_b200.reference_circuit(4, 2), 20),
+                                     (lambda: qris_b200.reference_circuit(2, 2), 20), (lambda: qris_b200.reference_circuit(6, 3).pinned("wide"), 300)])
 def test_backward_from_saved_state_matches_recompute(make, B):
     """qnn_forward_save / qnn_backward_saved (the autograd pair) against qnn_forward / qnn_backward."""
     circ = make()
@@ -300,7 +348,7 @@ def test_backward_from_saved_state_matches_recompute(make, B):
     assert torch.equal(y0, y1)
     lib = qris_b200._lib.lib()
     nbytes = lib.qnn_state_bytes(circ.handle(0), B)
-    if circ.n_qubits < 5:
+    if circ.n_qubits < 3:
         assert state is None and nbytes == 0          # generic kernels recompute
     else:
         assert state is not None and state.numel() * 4 == nbytes and nbytes >= B * (8 << circ.n_qubits)

@@ -68,6 +68,21 @@ def test_cluster_programs_mix_local_and_global_exchanges(n, L, kind):
     assert exact == 1.0 if kind == "u3" else exact >= 0.5
 
 
+@pytest.mark.parametrize("n", [3, 4, 5, 6, 7, 8])
+def test_narrow_variant_programs(n):
+    """8 amplitudes per thread (3 register bits): the program small batches run; also the only one for n = 3, 4."""
+    for c in (qris_b200.reference_circuit(n, 3), qris_b200.u3cu3_circuit(n, 2)):
+        desc, _ = _check(c.pinned("narrow"), seed=n)
+        assert desc["kr"] == 3 and desc["tb"] == n - 3 and len(desc["exchanges"][0]["woff"]) == 8 if desc["exchanges"] else desc["kr"] == 3
+
+
+@pytest.mark.parametrize("n", [5, 9, 10, 12])
+def test_sixteen_per_thread_programs(n):
+    for c in (qris_b200.reference_circuit(n, 2), qris_b200.u3cu3_circuit(n, 2)):
+        desc, _ = _check(c.pinned("16-per-thread"), seed=n)
+        assert desc["kr"] == 4 and desc["wb"] == max(0, n - 9)
+
+
 @pytest.mark.parametrize("n", [5, 8, 10])
 def test_amplitude_encoder_program(n):
     """The (normalised) input row is the initial state, gathered into the program's initial layout."""
@@ -87,6 +102,8 @@ def test_irregular_program():
 
 
 def test_out_of_scope_circuits_report_why():
-    assert not qris_b200.reference_circuit(4, 1).describe()["ok"]
+    assert not qris_b200.reference_circuit(2, 1).describe()["ok"]
+    assert not qris_b200.reference_circuit(4, 1).pinned("wide").describe()["ok"]
+    assert qris_b200.reference_circuit(4, 1).describe()["kr"] == 3
     d = qris_b200.u3cu3_circuit(12, 1, encoder="amplitude").describe()
     assert not d["ok"] and "amplitude" in d["why_not"]

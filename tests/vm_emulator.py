@@ -30,7 +30,7 @@ def _matrix(kind, a):
 
 def _apply_reg(state, U, rbit, lane_mask=None, ctrl_rbit=None):
     """state[lane, j]; apply U on register bit rbit for the selected lanes / control register bit."""
-    j = np.arange(32)
+    j = np.arange(state.shape[1])
     j0 = j[(j >> rbit) & 1 == 0]
     if ctrl_rbit is not None:
         j0 = j0[(j0 >> ctrl_rbit) & 1 == 1]
@@ -43,14 +43,15 @@ def _apply_reg(state, U, rbit, lane_mask=None, ctrl_rbit=None):
 
 
 def check_conflict_free(base, off, writing=True, local=False):
-    if len(base) > 32 * 8 and not local:              # cluster geometry: L2 buffer; writes must be coalesced
+    NA = len(off)
+    if len(base) > 32 * 8 and not local and NA == 32:              # cluster geometry: L2 buffer; writes must be coalesced
         if writing:
             for j in range(0, 32, 5):
                 for w0 in range(0, len(base), 32):
                     blocks = {(base[l] ^ off[j]) // 256 for l in range(w0, w0 + 32)}
                     assert len(blocks) == 1, "a warp's exchange write is not one aligned 256-byte block"
         return
-    for j in range(32):
+    for j in range(NA):
         for half in range(0, len(base), 16):          # every half-warp of every warp of the group
             slots = {((base[l] ^ off[j]) // 8) % 16 for l in range(half, half + 16)}
             assert len(slots) == 16, "shared-memory bank conflict in an exchange"
@@ -91,11 +92,13 @@ def emulate_forward(desc, x, w):
     """x: (samples_per_warp, n_inputs); returns y (samples_per_warp, n)."""
     assert desc["ok"]
     n, tb, wb = desc["n"], desc["tb"], desc.get("wb", 0)
+    kr = desc.get("kr", 5)               # register bits: 2^kr amplitudes per thread
+    NA = 1 << kr
     G = 32 << wb                          # threads per group (one warp for n <= 10)
     T = 1 << tb                           # threads per sample
     spw = G // T if wb == 0 else 1
     assert x.shape[0] == spw
-    state = np.zeros((G, 32), complex)
+    state = np.zeros((G, NA), complex)
     if desc.get("amplitude"):
         # x row (first 2^n entries, zero padded), normalised, gathered into the initial layout
         ibw = desc["initial_bit_of_wire"]
@@ -105,8 +108,8 @@ def emulate_forward(desc, x, w):
             row[:kk] = x[s, :kk]
             row /= np.linalg.norm(row)
             for t in range(T):
-                for jj in range(32):
-                    p = jj | (t << 5)
+                for jj in range(NA):
+                    p = jj | (t << kr)
                     k = sum(((p >> ibw[w]) & 1) << (n - 1 - w) for w in range(n))
                     state[s * T + t, jj] = row[k]
     else:
@@ -141,31 +144,31 @@ def emulate_forward(desc, x, w):
                 par = np.array([bin(int(v) & aux).count("1") & 1 for v in lis], bool)
                 _apply_reg(state, U, a, lane_mask=par)
                 stats["cg_p"] += 1
-        elif kind == MOP_ROT5:
-            for k in range(5):
+        elif kind == MOP_ROT5:                    # rotations on all kr register bits
+            for k in range(kr):
                 co = desc["coef_ops"][idx + ((aux >> (3 * k)) & 7)]
                 _apply_reg(state, _matrix(co["kind"], [_angle(s_, v_, w) for s_, v_ in zip(co["src"], co["value"])]), k)
-            stats["g1"] += 5
+            stats["g1"] += kr
         elif kind == MOP_ROTX5:
-            for k in range(5):
+            for k in range(kr):
                 col = (idx >> (5 * k)) & 31
                 for s in range(spw):
                     _apply_reg(state, _matrix(RY, [x[s, col]]), k, lane_mask=(samp == s))
-            stats["g1"] += 5
+            stats["g1"] += kr
         elif kind == MOP_CU3_CHAIN:
-            for k in range(4):
+            for k in range(kr - 1):
                 co = desc["coef_ops"][idx + k]
                 ang = [_angle(s_, v_, w) for s_, v_ in zip(co["src"], co["value"])]
                 if not ((aux >> k) & 1):
                     ang[1] = 0.0
                 _apply_reg(state, _matrix(U3, ang), k + 1, ctrl_rbit=k)
-            stats["cg_l"] += 4
+            stats["cg_l"] += kr - 1
         elif kind in (MOP_DIAG, MOP_DIAG_REG):
             D = desc["diags"][aux]
             assert bool(D["is_reg"]) == (kind == MOP_DIAG_REG)
-            j = np.arange(32)
-            p = j[None, :] | (lis[:, None] << 5)         # physical index of (lane, j) within its sample
-            ang = np.zeros((G, 32))
+            j = np.arange(NA)
+            p = j[None, :] | (lis[:, None] << kr)        # physical index of (lane, j) within its sample
+            ang = np.zeros((G, NA))
             for tkind, src, value, bit0, bit1 in D["terms"]:
                 if tkind == 0:
                     z = 1 - 2 * ((p >> bit0) & 1)
@@ -175,7 +178,7 @@ def emulate_forward(desc, x, w):
                 else:                              # deferred CU3 post-phase: e^{i phi} where both bits are 1
                     ang += _angle(src, value, w) * (((p >> bit0) & 1) & ((p >> bit1) & 1))
                 if kind == MOP_DIAG_REG:
-                    assert bit0 < 5 and bit1 < 5
+                    assert bit0 < kr and bit1 < kr
             state *= np.exp(1j * ang)
             stats["diag" if kind == MOP_DIAG else "diag_reg"] += 1
         elif kind == MOP_XCHG:
@@ -195,25 +198,25 @@ def emulate_forward(desc, x, w):
             local = mode == 1
             check_conflict_free(X["wbase"], X["woff"], local=local)
             check_conflict_free(X["rbase"], X["roff"], writing=False, local=local)
-            size = 65536 if local else 8192 * (G // 32)
+            size = 65536 if local else 256 * NA * (G // 32)
             cta = (lambda l: l // 256) if local else (lambda l: 0)
             buf = {}
             for l in range(G):
-                for jj in range(32):
+                for jj in range(NA):
                     addr = X["wbase"][l] ^ X["woff"][jj]
                     assert addr % 8 == 0 and 0 <= addr < size and (cta(l), addr) not in buf
                     buf[(cta(l), addr)] = state[l, jj]
             new = np.empty_like(state)
             for l in range(G):
-                for jj in range(32):
+                for jj in range(NA):
                     new[l, jj] = buf[(cta(l), X["rbase"][l] ^ X["roff"][jj])]
             state = new
             stats["xchg"] += 1
         else:
             raise ValueError(f"unknown micro-op {kind}")
     prob = np.abs(state) ** 2
-    j = np.arange(32)
-    p = j[None, :] | (lis[:, None] << 5)
+    j = np.arange(NA)
+    p = j[None, :] | (lis[:, None] << kr)
     y = np.zeros((spw, n))
     for wire, bit in enumerate(desc["final_bit_of_wire"]):
         z = 1 - 2 * ((p >> bit) & 1)
