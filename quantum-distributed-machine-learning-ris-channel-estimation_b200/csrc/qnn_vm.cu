@@ -122,6 +122,9 @@ __global__ void k_vm_finalize(const float* __restrict__ partial, int n_ctas, int
                               const int32_t* __restrict__ slot_ptr, const int32_t* __restrict__ slot_idx,
                               float* __restrict__ gw) {
   __shared__ double sred[128];
+  // launched with programmatic stream serialization right behind the backward kernel: its CTAs may be resident
+  // early; they wait here until that kernel has completed and its partial sums are visible (a no-op otherwise)
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   const int i = blockIdx.x;
   double acc = 0.0;
   for (int e = slot_ptr[i]; e < slot_ptr[i + 1]; ++e) {
@@ -223,8 +226,9 @@ bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
     out->ws_cbuf = has_l2 ? ((size_t)out->n_clusters << (p.n + 5)) : 0;
     out->ws_cluster = align256(out->ws_cbuf + (size_t)out->n_clusters * (1 << p.wb) * 48 * sizeof(float));
   } else {
-    out->fwd_threads = kFwdThreads;
-    size_t sf = smem_bytes(p, n_ang_in, kFwdThreads / 32, false, false);
+    // narrow variants serve small batches: 8-warp CTAs in the forward pass too, so that a batch spreads over twice as many SMs
+    out->fwd_threads = p.kr < kR ? kBwdThreads : kFwdThreads;
+    size_t sf = smem_bytes(p, n_ang_in, out->fwd_threads / 32, false, false);
     if (sf > kSmemMax && p.wb > 0) {                               // large samples: fewer groups per CTA
       out->fwd_threads = kBwdThreads;
       sf = smem_bytes(p, n_ang_in, bwd_warps, false, false);
@@ -305,7 +309,7 @@ int forward(const qnn_circuit* c, const Program& p, const Plan& pl, const float*
   if (pl.cluster == 0) {
     const int64_t groups_per_cta = (pl.fwd_threads / 32) >> p.wb;
     const int64_t ctas = (n_batches(p, B) + groups_per_cta - 1) / groups_per_cta;
-    grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, (int64_t)c->num_sm * (p.kr < kR ? 2 : 1)));
+    grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctas, (int64_t)c->num_sm * (p.kr < kR ? 4 : 1)));
   }
   const LaunchCfg lc{grid, pl.fwd_threads, pl.cluster, pl.smem_fwd, st};
   return launch_variant(p, pl, false, a.state != nullptr, lc, a);
@@ -322,7 +326,16 @@ int backward(const qnn_circuit* c, const Program& p, const Plan& pl, const float
   rc = launch_variant(p, pl, true, a.state != nullptr, lc, a);
   if (rc) return rc;
   if (c->n_weights > 0) {
-    k_vm_finalize<<<c->n_weights, 128, 0, st>>>(a.partial, pl.grid, p.n_acc, p.d_slots, p.d_slot_ptr, p.d_slot_idx, gw);
+    // programmatic dependent launch: the finalize grid is set up while the backward kernel still runs (the launch
+    // latency of a dependent kernel is a visible share of a small batch's backward pass)
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(c->n_weights); cfg.blockDim = dim3(128); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+    cudaLaunchAttribute attr{};
+    attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr.val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = &attr; cfg.numAttrs = 1;
+    QNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_vm_finalize, (const float*)a.partial, (int)pl.grid, (int)p.n_acc, (const GradSlot*)p.d_slots,
+                                      (const int32_t*)p.d_slot_ptr, (const int32_t*)p.d_slot_idx, gw));
     QNN_CUDA_CHECK(cudaGetLastError());
   }
   return QNN_OK;

@@ -512,10 +512,13 @@ struct Smem {
 template <bool BWD, bool STATE, int GEOM, bool AMP, int KR = 5>
 __global__ void __launch_bounds__(BWD ? 256 : 512, (BWD && KR < 5) ? 2 : 1) k_vm(const VmArgs a) {
   constexpr int NA = 1 << KR;
+  // backward: let the finalize kernel behind this one (launched with programmatic stream serialization) be set up
+  // now; it waits for this grid's completion before it reads the partial sums
+  if constexpr (BWD) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   // GEOM 0 always runs with the full CTA (compile-time constants); the others may be launched with fewer warps
-  const int WARPS = GEOM == 0 ? (BWD ? 8 : 16) : (int)(blockDim.x >> 5);
+  const int WARPS = GEOM == 0 ? ((BWD || KR < 5) ? 8 : 16) : (int)(blockDim.x >> 5);   // narrow variants: 8-warp CTAs both ways
   constexpr bool MW = GEOM >= 1, CL = GEOM == 2;
   const int tb = a.tb, wbits = MW ? a.wb : 0;
   const int gwarps = 1 << wbits, G = 32 << wbits;          // warps / threads per group (one sample for n >= 10)

@@ -127,6 +127,37 @@ def test_float64_inputs_and_unbatched():
     assert y.shape == (4,) and y.dtype == torch.float64
 
 
+def test_graphed_call_replays_the_module_step():
+    """qris_b200.GraphedCall: forward + backward of the layer recorded once and replayed for new inputs gives what
+    the plain calls give (same kernels, same order), at the reference's call size."""
+    circ = qris_b200.reference_circuit(6, 3)
+    torch.manual_seed(1)
+    layer = qris_b200.QNNLayer(circ).cuda()
+    clf = torch.nn.Linear(6, 3).cuda()
+
+    def step(x, lab):
+        for p in list(layer.parameters()) + list(clf.parameters()) + [x]:
+            p.grad = None
+        loss = F.nll_loss(F.log_softmax(clf(layer(x)), dim=1), lab)
+        loss.backward()
+        return loss.detach(), layer.weights.grad, x.grad
+    g = torch.Generator().manual_seed(4)
+    x0 = torch.zeros(256, 6, device="cuda", requires_grad=True)
+    call = qris_b200.GraphedCall(step, (x0, torch.zeros(256, dtype=torch.long, device="cuda")))
+    for it in range(6):                              # three eager calls, the recording, two replays
+        x = (2 * torch.rand(256, 6, generator=g) - 1).cuda()
+        lab = torch.randint(0, 3, (256,), generator=g).cuda()
+        loss, gw, gx = (t.clone() for t in call(x, lab))
+        xe = x.clone().requires_grad_(True)
+        loss_e, gw_e, gx_e = step(xe, lab)
+        assert abs(loss.item() - loss_e.item()) < 1e-6
+        assert_close(gw.cpu().numpy(), gw_e.cpu().numpy(), rel=1e-6, scale=float(gw_e.abs().max()), what=f"gw, call {it}")
+        assert_close(gx.cpu().numpy(), gx_e.cpu().numpy(), rel=1e-6, scale=float(gx_e.abs().max()), what=f"gx, call {it}")
+    assert call.graph is not None
+    with pytest.raises(ValueError):
+        call(torch.zeros(8, 6, device="cuda"), torch.zeros(8, dtype=torch.long, device="cuda"))
+
+
 # ---- the reference's OWN file on the GPU --------------------------------------------------------------
 class NoisyOracleQLayer(torch.nn.Module):
     """Checker for the reference's noise-and-restore forward: evaluates the circuit with the oracle at
