@@ -517,7 +517,9 @@ def cfg1_record(ctx, steps=30):
     return {"name": "cfg1", "workload": "BASELINE configs[0]: the as-shipped training step (Run:341-369): QSC_P128 n=6 L=3, nine "
                                         "user batches of 256, one backward, AdamW; whole model (CNN front end + QNN + classifier + optimiser)",
             "metric": "qsc_optimiser_steps_per_sec", "unit": "steps/s", "n_gpus": 1, "steps": steps, "scaling": "none",
-            "value": modes["eager"]["steps_per_s"], "modes": modes,
+            # runner.train_QSC_P128's default for the as-shipped flags (no weight noise, no batch statistics): the nine
+            # user batches as one model call, launched eagerly; "eager" is the nine separate calls of Run:341-352
+            "value": modes["eager_concat_users"]["steps_per_s"], "default_mode": "eager_concat_users", "modes": modes,
             "roofline": {"bound": "launch/host (71.0 kflop per sample: SURVEY.md H5)", "unit": "TFLOP/s", "peak": FP32_PEAK_NOMINAL_TFLOPS,
                          "frac": modes["graph_concat_users"]["qnn_frac_of_fp32_roofline"],
                          "algorithmic_flops_per_sample": {"fwd": f_fwd, "bwd": f_bwd}}}
