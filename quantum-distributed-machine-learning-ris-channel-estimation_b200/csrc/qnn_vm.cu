@@ -219,10 +219,10 @@ bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
     if (out->smem_fwd > kSmemMax || out->smem_bwd > kSmemMax) return false;
     out->n_clusters = (int)std::max<int64_t>(1, std::min<int64_t>(B, max_active_clusters_g2(out->cluster, out->smem_bwd, c->device, c->num_sm)));
     out->grid = out->n_clusters * out->cluster;
-    // L2 exchange buffers (four state-sized slices per cluster) only for programs that still have L2 exchanges,
+    // L2 exchange buffers (four state-sized slices per cluster) for programs with exchanges across CTAs,
     // then the cross-CTA partial sums
     bool has_l2 = false;
-    for (const MicroOp& m : p.ops) has_l2 = has_l2 || (m.kind == MOP_XCHG && m.aux == 0);
+    for (const MicroOp& m : p.ops) has_l2 = has_l2 || (m.kind == MOP_XCHG && (m.aux == 0 || m.aux == 2));   // (2: lam of the backward pass)
     out->ws_cbuf = has_l2 ? ((size_t)out->n_clusters << (p.n + 5)) : 0;
     out->ws_cluster = align256(out->ws_cbuf + (size_t)out->n_clusters * (1 << p.wb) * 48 * sizeof(float));
   } else {

@@ -435,13 +435,18 @@ struct Builder {
     for (int i = 0; i < 5; ++i) u[i] = wimg[5 + i] & lowmask;     // low parts of the images of the writer's lane bits
     for (int keep = 5; keep >= 0; --keep) {
       // a maximal independent subset of the first `keep` lane images gets the contiguous-run treatment
+      // Lane images that are single reader REGISTER bits go first and so get slot bits 0, 1, ...: a reader's
+      // registers that differ in those bits then sit in one 32-byte sector (the backward pass reads lam through
+      // an L2 buffer with this map: four of its loads per sector instead of one).
       int sel[5], ns = 0;
       uint32_t chosen[13];
-      for (int i = 0; i < keep; ++i) {
-        if (!u[i]) continue;
-        chosen[ns] = u[i];
-        if (independent(chosen, ns + 1)) sel[ns++] = i;
-      }
+      for (int pass = 0; pass < 2; ++pass)
+        for (int i = 0; i < keep; ++i) {
+          const bool reg_unit = is_unit(u[i]) && ctz(u[i]) < kR && wimg[5 + i] == u[i];
+          if (!u[i] || reg_unit != (pass == 0)) continue;
+          chosen[ns] = u[i];
+          if (independent(chosen, ns + 1)) sel[ns++] = i;
+        }
       for (int attempt = 0; attempt < 4000; ++attempt) {
         uint32_t bm[13], tg[13];
         int nb = 0;

@@ -983,24 +983,40 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, (BWD && KR < 5) ? 2 : 1) k_vm
             if constexpr (CL) {
               if (op.aux == 2) {
                 // The inverse permutation has its own maps (entry pad[1]) so that here, too, stores are the remote
-                // side and loads stay in this CTA.  psi travels through buffer 0 and lam through buffer 1, each
-                // behind its own cluster barrier; the local exchanges of the reverse sweep use buffer 1 only.  So
-                // buffer 0 is written remotely after the lam barrier of the previous exchange (this CTA's psi loads
-                // from it precede that barrier) and buffer 1 after this exchange's psi barrier (which this CTA
-                // reaches after its local exchanges).  The lam stores overlap with the psi loads.
+                // side and loads stay in this CTA.  psi travels through distributed shared memory and lam, at the
+                // same time, through an L2 buffer of the workspace (same slot map: coalesced 256-byte stores,
+                // sector-sized loads): the cluster fabric and the L2 path each carry half of the traffic, behind ONE
+                // cluster barrier.  Both buffer pairs alternate from one such exchange to the next, and the local
+                // exchanges in between use the shared buffer received into last (as in the forward program).
                 const Exchange* Xb = S.exchanges + X->pad[1];
-                const uint32_t wa = S.xbase[Xb->base + tig], ra = S.xbase[Xb->base + G + tig] & 0xFFFFu;
-                dsmem_store_all(ps, S.xbuf, wa, Xb->woff);
-                cluster_arrive(); cluster_wait();
-                dsmem_store_all(ls, S.xbuf + 65536u, wa, Xb->woff);
-                smem_load_all(ps, S.xbuf, ra, Xb->roff);
-                cluster_arrive(); cluster_wait();
-                smem_load_all(ls, S.xbuf + 65536u, ra, Xb->roff);
+                const uint32_t wa = S.xbase[Xb->base + tig], ra = S.xbase[Xb->base + G + tig];
+                xpar ^= 1u; xl2 ^= 1u;
+                const uint32_t buf = S.xbuf + (xpar << 16);
+                unsigned char* const lbuf = cbuf + (size_t)(2 * xl2 + 1) * cbuf_one;
+                dsmem_store_all(ps, buf, wa, Xb->woff);
+#pragma unroll
+                for (int q = 0; q < NA / 4; ++q) {
+                  const uint4 o = *reinterpret_cast<const uint4*>(Xb->woff + 4 * q);
+                  stg64(lbuf, wa ^ o.x, ls[4 * q + 0].x, ls[4 * q + 0].y);
+                  stg64(lbuf, wa ^ o.y, ls[4 * q + 1].x, ls[4 * q + 1].y);
+                  stg64(lbuf, wa ^ o.z, ls[4 * q + 2].x, ls[4 * q + 2].y);
+                  stg64(lbuf, wa ^ o.w, ls[4 * q + 3].x, ls[4 * q + 3].y);
+                }
+                gsync();
+#pragma unroll
+                for (int q = 0; q < NA / 4; ++q) {     // the L2 loads first: their latency overlaps the shared-memory loads
+                  const uint4 o = *reinterpret_cast<const uint4*>(Xb->roff + 4 * q);
+                  ldg64(lbuf, ra ^ o.x, ls[4 * q + 0].x, ls[4 * q + 0].y);
+                  ldg64(lbuf, ra ^ o.y, ls[4 * q + 1].x, ls[4 * q + 1].y);
+                  ldg64(lbuf, ra ^ o.z, ls[4 * q + 2].x, ls[4 * q + 2].y);
+                  ldg64(lbuf, ra ^ o.w, ls[4 * q + 3].x, ls[4 * q + 3].y);
+                }
+                smem_load_all(ps, buf, ra & 0xFFFFu, Xb->roff);
               } else {
                 const uint32_t wa = S.xbase[X->base + G + tig], ra = S.xbase[X->base + tig];
                 if (op.aux == 1) {
-                  exchange(ps, S.xbuf + 65536u, wa, ra, X->roff, X->woff, csync);
-                  exchange(ls, S.xbuf + 65536u, wa, ra, X->roff, X->woff, csync);
+                  exchange(ps, S.xbuf + (xpar << 16), wa, ra, X->roff, X->woff, csync);
+                  exchange(ls, S.xbuf + (xpar << 16), wa, ra, X->roff, X->woff, csync);
                 } else {
                   xl2 ^= 1u;
                   unsigned char* b0 = cbuf + (size_t)(2 * xl2) * cbuf_one;
