@@ -45,7 +45,8 @@ size_t smem_bytes(const Program& p, int n_inputs, int warps, bool bwd, bool clus
   if (cluster) {   // + the two 64 KB buffers of the shared-memory exchanges (local and across CTAs), when the program has any
     bool has_shared = false;
     for (const Exchange& X : p.exchanges) has_shared = has_shared || X.pad[0] != 0;
-    return table_bytes(p, n_inputs, warps, bwd, true) + (has_shared ? 2 * 65536 : 0) + 64;
+    // (two alternating buffers in the backward kernel; the forward kernel keeps one, so that two of its CTAs fit on an SM)
+    return table_bytes(p, n_inputs, warps, bwd, true) + (has_shared ? (bwd ? 2 : 1) * 65536 : 0) + 64;
   }
   const size_t warp_buf = (size_t)256 << p.kr;               // 32 lanes x 2^kr amplitudes x 8 bytes
   const size_t group_buf = warp_buf << p.wb;
@@ -207,7 +208,7 @@ bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
   if (!p.ok) return false;
   const int bwd_warps = kBwdThreads / 32;
   const int n_ang_in = p.amplitude ? 0 : c->n_inputs;        // input columns that need per-warp scratch
-  out->cluster = 0; out->n_clusters = 0; out->ws_cluster = 0; out->ws_cbuf = 0;
+  out->cluster = 0; out->n_clusters = 0; out->n_clusters_fwd = 0; out->ws_cluster = 0; out->ws_cbuf = 0;
   out->threads = kBwdThreads;
   out->warps_per_cta = bwd_warps;
   if ((1 << p.wb) > bwd_warps) {
@@ -217,14 +218,16 @@ bool plan(const qnn_circuit* c, const Program& p, int64_t B, Plan* out) {
     out->smem_fwd = smem_bytes(p, n_ang_in, bwd_warps, false, true);
     out->smem_bwd = smem_bytes(p, n_ang_in, bwd_warps, true, true);
     if (out->smem_fwd > kSmemMax || out->smem_bwd > kSmemMax) return false;
-    out->n_clusters = (int)std::max<int64_t>(1, std::min<int64_t>(B, max_active_clusters_g2(out->cluster, out->smem_bwd, c->device, c->num_sm)));
+    out->n_clusters = (int)std::max<int64_t>(1, std::min<int64_t>(B, max_active_clusters_g2(out->cluster, out->smem_bwd, c->device, c->num_sm, true)));
+    out->n_clusters_fwd = (int)std::max<int64_t>(1, std::min<int64_t>(B, max_active_clusters_g2(out->cluster, out->smem_fwd, c->device, c->num_sm, false)));
     out->grid = out->n_clusters * out->cluster;
     // L2 exchange buffers (four state-sized slices per cluster) for programs with exchanges across CTAs,
     // then the cross-CTA partial sums
     bool has_l2 = false;
     for (const MicroOp& m : p.ops) has_l2 = has_l2 || (m.kind == MOP_XCHG && (m.aux == 0 || m.aux == 2));   // (2: lam of the backward pass)
-    out->ws_cbuf = has_l2 ? ((size_t)out->n_clusters << (p.n + 5)) : 0;
-    out->ws_cluster = align256(out->ws_cbuf + (size_t)out->n_clusters * (1 << p.wb) * 48 * sizeof(float));
+    const size_t ncl = (size_t)std::max(out->n_clusters, out->n_clusters_fwd);
+    out->ws_cbuf = has_l2 ? (ncl << (p.n + 5)) : 0;
+    out->ws_cluster = align256(out->ws_cbuf + ncl * (1 << p.wb) * 48 * sizeof(float));
   } else {
     // narrow variants serve small batches: 8-warp CTAs in the forward pass too, so that a batch spreads over twice as many SMs
     out->fwd_threads = p.kr < kR ? kBwdThreads : kFwdThreads;
@@ -305,7 +308,7 @@ int forward(const qnn_circuit* c, const Program& p, const Plan& pl, const float*
   a.x = x; a.y = y; a.B = B; a.state = reinterpret_cast<float4*>(state); a.w = w;
   int rc = launch_prep(p, w, a, st);
   if (rc) return rc;
-  int grid = pl.grid;
+  int grid = pl.cluster > 0 ? pl.n_clusters_fwd * pl.cluster : pl.grid;
   if (pl.cluster == 0) {
     const int64_t groups_per_cta = (pl.fwd_threads / 32) >> p.wb;
     const int64_t ctas = (n_batches(p, B) + groups_per_cta - 1) / groups_per_cta;

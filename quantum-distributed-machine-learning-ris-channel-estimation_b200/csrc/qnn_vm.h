@@ -123,7 +123,8 @@ std::string describe(const Program& p);   // JSON, for tests and introspection
 
 struct Plan {
   int threads, grid, warps_per_cta, fwd_threads;
-  int cluster, n_clusters;               // CTAs per sample for n >= 14 (0: no cluster), clusters in the grid
+  int cluster, n_clusters;               // CTAs per sample for n >= 14 (0: no cluster), clusters in the backward grid
+  int n_clusters_fwd;                    // clusters in the forward grid (two forward CTAs fit on an SM)
   size_t ws_cluster;                     // L2 exchange buffers (ws_cbuf, if the program has L2 exchanges) + cross-CTA scratch
   size_t ws_cbuf;
   size_t smem_fwd, smem_bwd;

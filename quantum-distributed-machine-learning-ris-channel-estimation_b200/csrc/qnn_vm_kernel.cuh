@@ -774,7 +774,10 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, (BWD && KR < 5) ? 2 : 1) k_vm
                 // to the next and the local exchanges in between use the one received into last, so ONE cluster
                 // barrier per exchange suffices: a buffer is written remotely only by CTAs that have passed the
                 // barrier of the exchange in between, which this CTA reaches after its last use of that buffer.
-                xpar ^= 1u;
+                // The forward kernel keeps ONE buffer (so that two of its CTAs, of different clusters, fit on an SM and
+                // hide each other's barrier and exchange latency): a second cluster barrier in front of the stores
+                // then makes sure every CTA of the cluster is done with its previous use of the buffer.
+                if constexpr (!BWD) gsync(); else xpar ^= 1u;
                 const uint32_t buf = S.xbuf + (xpar << 16);
                 dsmem_store_all(ps, buf, S.xbase[X->base + tig], X->woff);
                 gsync();
@@ -1124,6 +1127,6 @@ int launch_g1_k4(bool bwd, bool state, const LaunchCfg& lc, const VmArgs& a);  /
 int launch_g0a(bool bwd, bool state, const LaunchCfg& lc, const VmArgs& a);   // n <= 10, amplitude encoder
 int launch_g1(bool bwd, bool state, const LaunchCfg& lc, const VmArgs& a);    // n = 11..13
 int launch_g2(bool bwd, bool state, const LaunchCfg& lc, const VmArgs& a);    // n = 14..16 (clusters)
-int max_active_clusters_g2(int cluster, size_t smem, int device, int num_sm);
+int max_active_clusters_g2(int cluster, size_t smem, int device, int num_sm, bool bwd);
 
 }  // namespace vm
