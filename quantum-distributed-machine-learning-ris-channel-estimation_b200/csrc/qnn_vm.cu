@@ -55,8 +55,9 @@ size_t smem_bytes(const Program& p, int n_inputs, int warps, bool bwd, bool clus
 
 // ---- per-call tables: gate coefficients (double-precision trig) and merged diagonals -----------------
 // Grid: coef_blocks CTAs for the coefficient rows, then `chunks` CTAs per diagonal, each filling kPrepChunk
-// entries of its table (a 16-qubit table has 65,536 entries: one CTA per table took ~0.9 ms per call).
-constexpr int kPrepThreads = 128, kPrepChunk = 1024, kPrepTermTile = 64;
+// entries of its table (a 16-qubit table has 65,536 entries: one CTA per table took ~0.9 ms per call; two entries per
+// thread keep the fill at a few microseconds, which matters when a rank's share of the batch is small).
+constexpr int kPrepThreads = 128, kPrepChunk = 256, kPrepTermTile = 64;
 __global__ void __launch_bounds__(kPrepThreads)
 k_vm_prep(const DevOp* __restrict__ coef_ops, int n_coef, const DiagDesc* __restrict__ diags, int n_diags,
           const DiagTerm* __restrict__ terms, const float* __restrict__ w, int tb, int wbits, int kr, float* __restrict__ coef,
