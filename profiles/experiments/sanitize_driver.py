@@ -16,10 +16,24 @@ import torch  # noqa: E402
 
 import qris_b200  # noqa: E402
 
+if "--checked" in sys.argv:
+    # the self-checking build (make -C .../csrc checked): every exchange address is checked on the device and a
+    # violation prints "QNN_VM_CHECKS: violation ..." (grep the output for it)
+    sys.argv.remove("--checked")
+    qris_b200._lib.LIB_PATH = os.path.join(os.path.dirname(qris_b200._lib.LIB_PATH), "libqnn_b200_checked.so")
+    print("using", qris_b200._lib.LIB_PATH, flush=True)
+
 cases = [("u3cu3 n=8", qris_b200.u3cu3_circuit(8, 2), 9), ("ref n=6", qris_b200.reference_circuit(6, 3), 37),
          ("u3cu3 n=12", qris_b200.u3cu3_circuit(12, 2), 5), ("u3cu3 n=14", qris_b200.u3cu3_circuit(14, 2), 3),
          ("u3cu3 n=16", qris_b200.u3cu3_circuit(16, 2), 2), ("amplitude n=8", qris_b200.u3cu3_circuit(8, 1, encoder="amplitude"), 7),
-         ("generic n=7", qris_b200.u3cu3_circuit(7, 1).generic(), 5), ("generic n=12", qris_b200.reference_circuit(12, 1).generic(), 2)]
+         ("generic n=7", qris_b200.u3cu3_circuit(7, 1).generic(), 5), ("generic n=12", qris_b200.reference_circuit(12, 1).generic(), 2),
+         ("narrow n=6", qris_b200.reference_circuit(6, 3).pinned("narrow"), 301), ("narrow n=3", qris_b200.u3cu3_circuit(3, 2), 70),
+         ("narrow n=8", qris_b200.u3cu3_circuit(8, 3).pinned("narrow"), 37), ("wide n=6", qris_b200.reference_circuit(6, 3).pinned("wide"), 301),
+         ("16-per-thread n=10", qris_b200.u3cu3_circuit(10, 2).pinned("16-per-thread"), 9),
+         ("16-per-thread n=12", qris_b200.reference_circuit(12, 2).pinned("16-per-thread"), 3),
+         ("ref n=10", qris_b200.reference_circuit(10, 3), 70), ("u3cu3 n=13", qris_b200.u3cu3_circuit(13, 3), 20),
+         ("ref n=15", qris_b200.reference_circuit(15, 2), 40), ("u3cu3 n=16 L=8", qris_b200.u3cu3_circuit(16, 8), 40),
+         ("ref n=16", qris_b200.reference_circuit(16, 3), 37), ("deep n=14 (L2 exchanges only)", qris_b200.u3cu3_circuit(14, 20), 3)]
 only = sys.argv[1:] if len(sys.argv) > 1 else None
 for name, circ, B in cases:
     if only and not any(o in name for o in only):

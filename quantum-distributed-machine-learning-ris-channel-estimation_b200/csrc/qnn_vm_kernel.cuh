@@ -83,6 +83,24 @@ __device__ __forceinline__ double diag_angle(const DiagDesc& D, const DiagTerm* 
   return ang;
 }
 
+// ---- optional self-checks (make checked: -DQNN_VM_CHECKS -> libqnn_b200_checked.so) ----------------------------
+// compute-sanitizer is not available on the GPU pool this was developed on; this build checks every exchange
+// address against the bounds of the buffer it must fall into (alignment, window, destination CTA) on the device and
+// prints violations (`QNN_VM_CHECKS: violation ...`; profiles/experiments/sanitize_driver.py looks for that line).  Not
+// compiled into the product library.
+#ifdef QNN_VM_CHECKS
+static __device__ unsigned long long g_vm_check_failures = 0ULL;   // (one per translation unit: only limits the printing)
+__device__ __forceinline__ void vm_check(bool ok, int code, uint32_t v) {
+  if (!ok && atomicAdd(&g_vm_check_failures, 1ULL) < 8ULL)
+    printf("QNN_VM_CHECKS: violation %d (value 0x%x) block %d thread %d\n", code, v, (int)blockIdx.x, (int)threadIdx.x);
+}
+// all NA addresses base ^ off[j] (byte offsets relative to `lo`) are 8-byte aligned and below `size`
+#define VM_CHECK_OFFSETS(CODE, BASE, OFFS, SIZE)                                                     \
+  for (int j_ = 0; j_ < NA; ++j_) { const uint32_t v_ = (uint32_t)(BASE) ^ (OFFS)[j_]; vm_check((v_ & 7u) == 0u && v_ < (uint32_t)(SIZE), CODE, v_); }
+#else
+#define VM_CHECK_OFFSETS(CODE, BASE, OFFS, SIZE)
+#endif
+
 // ---- shared-memory access by 32-bit shared address (XOR addressing needs integer addresses) --------
 __device__ __forceinline__ void sts64(uint32_t addr, float a, float b) {
   asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
@@ -768,6 +786,7 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, (BWD && KR < 5) ? 2 : 1) k_vm
             const Exchange* X = S.exchanges + op.idx;
             if constexpr (CL) {
               if (op.aux == 1) {   // local: the CTA bits stay put, the exchange runs through this CTA's shared memory
+                VM_CHECK_OFFSETS(1, S.xbase[X->base + tig], X->woff, 65536u) VM_CHECK_OFFSETS(2, S.xbase[X->base + G + tig], X->roff, 65536u)
                 exchange(ps, S.xbuf + (xpar << 16), S.xbase[X->base + tig], S.xbase[X->base + G + tig], X->woff, X->roff, csync);
               } else if (op.aux == 2) {
                 // Across CTAs through distributed shared memory.  The two buffers alternate from one such exchange
@@ -779,15 +798,21 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, (BWD && KR < 5) ? 2 : 1) k_vm
                 // then makes sure every CTA of the cluster is done with its previous use of the buffer.
                 if constexpr (!BWD) gsync(); else xpar ^= 1u;
                 const uint32_t buf = S.xbuf + (xpar << 16);
+                VM_CHECK_OFFSETS(3, S.xbase[X->base + tig], X->woff, (uint32_t)a.cluster << 16)       // destination rank < cluster size
+                VM_CHECK_OFFSETS(4, S.xbase[X->base + G + tig] ^ (crank << 16), X->roff, 65536u)    // loads stay in this CTA
                 dsmem_store_all(ps, buf, S.xbase[X->base + tig], X->woff);
                 gsync();
                 smem_load_all(ps, buf, S.xbase[X->base + G + tig] & 0xFFFFu, X->roff);
               } else {
                 xl2 ^= 1u;
                 unsigned char* b0 = cbuf + (size_t)(2 * xl2) * cbuf_one;
+                VM_CHECK_OFFSETS(5, S.xbase[X->base + tig], X->woff, cbuf_one) VM_CHECK_OFFSETS(6, S.xbase[X->base + G + tig], X->roff, cbuf_one)
                 exchange_global<false>(ps, ps, b0, b0, S.xbase[X->base + tig], S.xbase[X->base + G + tig], X->woff, X->roff, gsync);
               }
-            } else exchange(ps, 0u, S.xbuf | S.xbase[X->base + tig], S.xbuf | S.xbase[X->base + G + tig], X->woff, X->roff, gsync);
+            } else {
+              VM_CHECK_OFFSETS(7, S.xbase[X->base + tig], X->woff, (256u * NA) << wbits) VM_CHECK_OFFSETS(8, S.xbase[X->base + G + tig], X->roff, (256u * NA) << wbits)
+              exchange(ps, 0u, S.xbuf | S.xbase[X->base + tig], S.xbuf | S.xbase[X->base + G + tig], X->woff, X->roff, gsync);
+            }
           } break;
           default: break;
         }
@@ -996,6 +1021,8 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, (BWD && KR < 5) ? 2 : 1) k_vm
                 xpar ^= 1u; xl2 ^= 1u;
                 const uint32_t buf = S.xbuf + (xpar << 16);
                 unsigned char* const lbuf = cbuf + (size_t)(2 * xl2 + 1) * cbuf_one;
+                VM_CHECK_OFFSETS(9, wa, Xb->woff, (uint32_t)a.cluster << 16) VM_CHECK_OFFSETS(10, ra ^ (crank << 16), Xb->roff, 65536u)
+                VM_CHECK_OFFSETS(11, wa, Xb->woff, cbuf_one) VM_CHECK_OFFSETS(12, ra, Xb->roff, cbuf_one)
                 dsmem_store_all(ps, buf, wa, Xb->woff);
 #pragma unroll
                 for (int q = 0; q < NA / 4; ++q) {
@@ -1018,16 +1045,19 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, (BWD && KR < 5) ? 2 : 1) k_vm
               } else {
                 const uint32_t wa = S.xbase[X->base + G + tig], ra = S.xbase[X->base + tig];
                 if (op.aux == 1) {
+                  VM_CHECK_OFFSETS(13, wa, X->roff, 65536u) VM_CHECK_OFFSETS(14, ra, X->woff, 65536u)
                   exchange(ps, S.xbuf + (xpar << 16), wa, ra, X->roff, X->woff, csync);
                   exchange(ls, S.xbuf + (xpar << 16), wa, ra, X->roff, X->woff, csync);
                 } else {
                   xl2 ^= 1u;
                   unsigned char* b0 = cbuf + (size_t)(2 * xl2) * cbuf_one;
+                  VM_CHECK_OFFSETS(15, wa, X->roff, cbuf_one) VM_CHECK_OFFSETS(16, ra, X->woff, cbuf_one)
                   exchange_global<true>(ps, ls, b0, b0 + cbuf_one, wa, ra, X->roff, X->woff, gsync);
                 }
               }
             } else {
               const uint32_t wa = S.xbuf | S.xbase[X->base + G + tig], ra = S.xbuf | S.xbase[X->base + tig];
+              VM_CHECK_OFFSETS(17, wa ^ S.xbuf, X->roff, (256u * NA) << wbits) VM_CHECK_OFFSETS(18, ra ^ S.xbuf, X->woff, (256u * NA) << wbits)
               exchange(ps, 0u, wa, ra, X->roff, X->woff, gsync);
               exchange(ls, 0u, wa, ra, X->roff, X->woff, gsync);
             }
