@@ -117,6 +117,31 @@ def test_amplitude_encoder_ragged_batches_are_finite(n, n_inputs, B):
         assert yz[B // 2].abs().max() == 0 and gxz[B // 2].abs().max() == 0
 
 
+@pytest.mark.parametrize("n,L,B", [(14, 6, 300), (15, 4, 150), (16, 4, 90)])
+def test_cluster_exchanges_are_deterministic_under_load(n, L, B):
+    """Many samples per cluster and two forward clusters per SM: the alternating shared-memory buffers, the second
+    cluster barrier of the forward kernel and the L2 slices of the backward pass are reused hundreds of times.  A race
+    in that protocol would show as run-to-run differences: three runs must agree bit for bit (plain pair and
+    saved-state pair), sampled rows must match the oracle, and the result must not depend on which rows share a call."""
+    circ = qris_b200.u3cu3_circuit(n, L)
+    x, w, gy = (t.cuda() for t in seeded_inputs(circ, B, seed=n * L))
+    runs = []
+    for _ in range(3):
+        y, state = qris_b200.qnn_forward_raw(circ, x, w, save_state=True)
+        gx, gw = qris_b200.qnn_backward_raw(circ, x, w, gy, state=state)
+        gx2, gw2 = qris_b200.qnn_backward_raw(circ, x, w, gy)
+        runs.append((y.clone(), gx.clone(), gw.clone(), gx2.clone(), gw2.clone()))
+    for r in runs[1:]:
+        assert all(torch.equal(a, b) for a, b in zip(r, runs[0]))
+    idx = torch.tensor([0, B // 2, B - 1])
+    yo, gxo, _ = O.forward_and_grads(oracle_ops(circ), n, x[idx].cpu(), w.cpu(), gy[idx].cpu())
+    assert_close(runs[0][0][idx].cpu().numpy(), yo.numpy(), what="rows y")
+    assert_close(runs[0][1][idx].cpu().numpy(), gxo.numpy(), scale=float(gxo.abs().max()), what="rows gx")
+    ys = qris_b200.qnn_forward_raw(circ, x[idx.cuda()].contiguous(), w)
+    assert torch.equal(ys, runs[0][0][idx.cuda()])
+    assert_close(runs[0][4].cpu().numpy(), runs[0][2].cpu().numpy(), rel=2e-5, scale=float(runs[0][2].abs().max()), what="gw recompute vs saved")
+
+
 def test_deep_cluster_circuit_falls_back_to_l2_exchanges():
     """Programs whose tables leave no room for the 64 KB local-exchange buffer are compiled with L2
     exchanges only and still run on the VM."""
