@@ -203,9 +203,9 @@ def test_survey_fixed_vector_and_closed_form():
     assert_close(y1, O.ref_circuit_L1_closed_form(xx, ww), what="closed form")
 
 
-@pytest.mark.parametrize("kind,n,L,B", [("ref", 6, 3, 4096), ("u3", 10, 3, 65536)])
+@pytest.mark.parametrize("kind,n,L,B", [("ref", 6, 3, 4096), ("u3", 10, 3, 65536), ("u3", 16, 8, 576)])
 def test_full_size_properties(kind, n, L, B):
-    """BASELINE configs 2 and 3 at full batch: properties that need no oracle run of that size."""
+    """BASELINE configs 2, 3 and 4 at full batch: properties that need no oracle run of that size."""
     circ = qris_b200.reference_circuit(n, L) if kind == "ref" else qris_b200.u3cu3_circuit(n, L)
     x, w, gy = seeded_inputs(circ, B, seed=42)
     dev = torch.device("cuda:0")
@@ -217,7 +217,7 @@ def test_full_size_properties(kind, n, L, B):
     idx = torch.tensor([0, 1, B // 3, B // 2 + 1, B - 1], device=dev)
     ys = qris_b200.qnn_forward_raw(circ, xd[idx].contiguous(), wd)
     gxs, _ = qris_b200.qnn_backward_raw(circ, xd[idx].contiguous(), wd, gd[idx].contiguous())
-    assert torch.equal(ys, y[idx]) and torch.allclose(gxs, gx[idx], atol=1e-6)
+    assert torch.equal(ys, y[idx]) and torch.allclose(gxs, gx[idx], atol=1e-6 if n <= 10 else 2e-5)
     # (2) those rows agree with the oracle
     yo, gxo, _ = O.forward_and_grads(oracle_ops(circ), n, x[idx.cpu()], w, gy[idx.cpu()])
     assert_close(ys.cpu().numpy(), yo.numpy(), what="rows y")
@@ -237,7 +237,7 @@ def test_full_size_properties(kind, n, L, B):
         assert gw.reshape(L, n, 2)[L - 1, :, 1].abs().max().item() <= 1e-3 * scale
     # (6) the batch reduction itself: gw of a contiguous 2,048-sample slice, taken from inside the full batch so
     #     that several CTAs and the finalize kernel take part, against the oracle's gw of the same rows
-    lo, cnt = B // 4 + 3, min(2048, B // 2)
+    lo, cnt = B // 4 + 3, (min(2048, B // 2) if n <= 10 else 3)      # (a 16-qubit, 8-layer oracle row takes seconds)
     _, gws = qris_b200.qnn_backward_raw(circ, xd[lo:lo + cnt].contiguous(), wd, gd[lo:lo + cnt].contiguous(), need_gx=False)
     _, _, gwo = O.forward_and_grads(oracle_ops(circ), n, x[lo:lo + cnt], w, gy[lo:lo + cnt])
     assert_close(gws.cpu().numpy(), gwo.numpy(), scale=float(gwo.abs().max()), what="gw of a 2048-row slice")
