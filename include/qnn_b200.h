@@ -139,7 +139,7 @@ QNN_API int qnn_backward_saved(const qnn_circuit* c, const float* x, const float
                                size_t workspace_bytes, void* cuda_stream);
 
 /* No counterpart in the reference.  Same gradients as qnn_backward (always computed by the generic kernel
- * family, so for n = 5..16 they agree with qnn_backward's register-resident kernels to rounding, not bit for
+ * family, so for n = 3..16 they agree with qnn_backward's register-resident kernels to rounding, not bit for
  * bit, and take several times longer), for callers that cannot supply a
  * workspace because they may not allocate device memory once running: real-time loops (a per-slot
  * channel-estimation service) where cudaMalloc's device-wide synchronisation and unbounded latency

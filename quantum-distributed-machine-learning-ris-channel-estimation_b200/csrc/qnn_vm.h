@@ -6,7 +6,7 @@
 // one warp, which then carries 32 / 2^TB samples and always 1024 amplitudes; for n = 11..13 a sample spans
 // 2^(n-10) warps of one CTA (a "group"), which exchange through a group-wide shared buffer and a named barrier;
 // for n = 14..16 the group is a thread-block cluster of 2..8 CTAs (a sample needs the registers of several
-// SMs), exchanging through an L2-resident buffer in the workspace with cluster barriers.  A *layout* says which logical wire sits on which
+// SMs), exchanging through (distributed) shared memory with cluster barriers.  A *layout* says which logical wire sits on which
 // physical bit; gates act only on register bits, and an EXCHANGE micro-op re-lays the state out
 // through a warp-private shared-memory buffer with GF(2)-linear, bank-conflict-free addressing.
 // CNOTs cost nothing: they update the layout matrix and are materialised by the next exchange.
@@ -75,7 +75,7 @@ struct DiagDesc {      // per DIAG / DIAG_REG micro-op
   int32_t acc_thr[kMaxThreadBits];   // same for thread bits (lane bits first, then warp bits)
 };
 
-struct Exchange {      // byte offsets into the group's buffer (8 KB per warp); address = base[thread] ^ off[j]
+struct Exchange {      // byte offsets into the group's buffer (256 * 2^kr bytes per warp); address = base[thread] ^ off[j]
   uint32_t woff[32], roff[32];
   uint32_t base;       // first of 2 * G entries in Program::xbase (G = threads per group): write bases, then read bases
   uint32_t pad[3];     // pad[0]: 0 plain / L2, 1 local exchange of the cluster geometry, 2 distributed shared memory

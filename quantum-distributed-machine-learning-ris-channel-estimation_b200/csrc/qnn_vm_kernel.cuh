@@ -1,7 +1,7 @@
 // Register-resident statevector VM kernels (program format: qnn_vm.h, compiler: qnn_vm_compile.cpp).
 //
 // One warp carries 1024 amplitudes (32 / 2^tb samples of n = 5 + tb qubits); every lane keeps 32 complex
-// amplitudes in registers.  The kernel is a persistent interpreter: per micro-op one warp-uniform switch
+// amplitudes in registers (the narrow variants: 8 or 16 per lane, template parameter KR).  The kernel is a persistent interpreter: per micro-op one warp-uniform switch
 // selects a fully unrolled body specialised on the register bit(s) it touches, so all state indexing is
 // static and the state never leaves the register file except in EXCHANGE, which re-lays it out through a
 // warp-private 8 KB shared buffer with XOR (GF(2)-linear) addressing that is bank-conflict free on both
@@ -521,7 +521,8 @@ struct Smem {
 
 // GEOM 0: a warp carries whole samples (n <= 10): constant strides, __syncwarp barriers.
 // GEOM 1: a sample spans 2^wb warps of one CTA (n = 11..13): shared exchange buffer, named barriers.
-// GEOM 2: a sample spans a thread-block cluster (n = 14..16): exchange buffer in L2, cluster barriers,
+// GEOM 2: a sample spans a thread-block cluster (n = 14..16): exchanges through the CTA's own or, across CTAs,
+//         distributed shared memory (L2 buffers as the fallback and for lam in the backward pass), cluster barriers,
 //         per-thread bases and cross-CTA partial sums in global memory.
 // AMP: amplitude encoder (GEOM 0 only); a separate instantiation keeps its gather/scatter code and live
 // values out of the angle-encoder kernels.
