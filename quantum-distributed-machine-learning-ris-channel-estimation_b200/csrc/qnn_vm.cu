@@ -161,7 +161,7 @@ void fill_args(const qnn_circuit* c, const Program& p, const Plan& pl, void* ws,
   a->n = p.n; a->tb = p.tb; a->wb = p.wb; a->n_inputs = c->n_inputs; a->n_acc = p.n_acc;
   a->cluster = pl.cluster;
   a->inline_prep = inline_prep(p) ? 1 : 0;
-  a->coef_ops = p.d_coef_ops; a->terms = p.d_terms; a->n_terms = (int)p.terms.size();
+  a->coef_ops = p.d_coef_ops; a->terms = p.d_terms; a->n_terms = (int)p.terms.size(); a->n_w = c->n_weights;
   a->amplitude = p.amplitude ? 1 : 0;
   a->n_angle = p.amplitude ? 0 : c->n_inputs;
   for (int w = 0; w < 16; ++w) a->init_bit_of_wire[w] = w < p.n ? (int8_t)p.initial_bit_of_wire[w] : 0;

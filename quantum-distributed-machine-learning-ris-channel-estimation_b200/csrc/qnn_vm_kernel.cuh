@@ -50,7 +50,7 @@ struct VmArgs {
   // narrow variants: the per-call tables (coefficient rows, diagonals) are made in the kernel's prologue by every
   // CTA instead of by a k_vm_prep launch (small programs, small batches: the launch costs more than the work)
   int inline_prep;
-  const DevOp* coef_ops; const DiagTerm* terms; const float* w; int n_terms;
+  const DevOp* coef_ops; const DiagTerm* terms; const float* w; int n_terms, n_w;
 };
 
 // ---- per-call tables: gate coefficients and merged diagonals (double-precision trig) -------------------------
@@ -66,6 +66,7 @@ __device__ __forceinline__ void make_coef_row(const DevOp& op, const float* __re
   row[1] = (float)sin(phi);
   row[2] = (((long long)k) & 1LL) ? -1.f : 1.f;
   row[3] = 0.f;
+  if (op.nang < 3) { row[4] = 1.f; row[5] = 0.f; row[6] = 1.f; row[7] = 0.f; return; }   // plain rotation: no phases
   double sl, cl, sp, cp;
   sincos(a[2], &sl, &cl);
   sincos(a[1], &sp, &cp);
@@ -587,6 +588,30 @@ __global__ void __launch_bounds__(BWD ? 256 : 512, (BWD && KR < 5) ? 2 : 1) k_vm
     const uint32_t* src; uint32_t* dst; int words;
     bool inl = false;
     if constexpr (KR < 5) inl = a.inline_prep != 0;
+    if constexpr (KR < 5) {
+      // Small batches: the prologue below reads half a dozen small arrays one after the other, each a cold miss (the
+      // caller's other kernels have flushed them out of L2 since the last call), some of them dependent (terms -> w).
+      // One round of prefetches brings all of them, and this CTA's first input rows, towards L2 at once.
+      auto prefetch = [&](const void* base, size_t bytes) {
+        for (size_t o = (size_t)tid * 128; o < bytes; o += (size_t)blockDim.x * 128)
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(base) + o));
+      };
+      prefetch(a.ops, (size_t)a.n_ops * sizeof(MicroOp));
+      prefetch(a.exchanges, (size_t)a.n_exchanges * sizeof(Exchange));
+      prefetch(a.xbase, (size_t)a.n_xbase * 4);
+      prefetch(a.diags, (size_t)a.n_diags * sizeof(DiagDesc));
+      if (inl) {
+        prefetch(a.terms, (size_t)a.n_terms * sizeof(DiagTerm));
+        prefetch(a.coef_ops, (size_t)a.n_coef * sizeof(DevOp));
+        prefetch(a.w, (size_t)a.n_w * 4);
+      }
+      const size_t row0 = (size_t)blockIdx.x * WARPS * spw;     // first sample of this CTA
+      if ((long long)row0 < a.B) {
+        const size_t rows = min((size_t)(a.B - (long long)row0), (size_t)WARPS * spw);
+        prefetch(a.x + row0 * a.n_inputs, rows * a.n_inputs * 4);
+        if (BWD) prefetch(a.gy + row0 * a.n, rows * a.n * 4);
+      }
+    }
     if (!inl) {
       for (int i = tid; i < a.n_ops; i += blockDim.x) {
         const MicroOp m = a.ops[i];
