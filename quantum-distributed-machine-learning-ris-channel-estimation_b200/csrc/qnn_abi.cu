@@ -224,8 +224,11 @@ static const vm::Program* vm_plan(const qnn_circuit* c, int64_t B, vm::Plan* pl)
     const int64_t spw = c->vm->wb ? 1 : (32 >> c->vm->tb);
     narrow = (c->flags & QNN_CREATE_NARROW_ONLY) || (B + spw - 1) / spw <= (int64_t)c->num_sm * 2;
   }
-  const vm::Program* prog = narrow ? c->vm_narrow : c->vm;
-  return (prog && vm::plan(c, *prog, B, pl)) ? prog : nullptr;
+  const vm::Program* first = narrow ? c->vm_narrow : c->vm;
+  const vm::Program* second = narrow ? c->vm : c->vm_narrow;
+  if (first && first->ok && vm::plan(c, *first, B, pl)) return first;
+  if ((c->flags & (QNN_CREATE_NARROW_ONLY | QNN_CREATE_WIDE_ONLY)) == 0 && second && second->ok && vm::plan(c, *second, B, pl)) return second;
+  return nullptr;
 }
 
 extern "C" const char* qnn_circuit_plan(const qnn_circuit* c, int64_t B) {
